@@ -1,0 +1,190 @@
+"""ctypes binding of the depthconv_b200 C ABI (include/depthconv_b200.h).
+
+Used by the tests, bench.py and __graft_entry__.py. The directory name carries
+a hyphen, so import it with `importlib` (see `tests/conftest.py::load_pkg`) or
+via `__graft_entry__.load_pkg()`; the module registers itself as
+`depth_conversions_b200`.
+
+There is no fallback: if the CUDA library is missing or no B200 is present,
+loading / context creation raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "lib", "libdepthconv_b200.so")
+HOST_LIB_PATH = os.path.join(HERE, "lib", "libdc_host.so")
+DEPTH2X_PATH = os.path.join(HERE, "bin", "depth2x")
+
+# enums of include/depthconv_b200.h
+DC_RANGE, DC_BEARING, DC_FLEXION, DC_CURVATURE, DC_MAX_CURVE, DC_SCALE = range(6)
+DC_IN_U16_DEPTH, DC_IN_U16_RANGE, DC_IN_F32_RANGE = range(3)
+DC_OUT_F32, DC_OUT_U16 = range(2)
+DC_OK, DC_ERR_INVALID, DC_ERR_NO_DEVICE, DC_ERR_CUDA = 0, -1, -2, -3
+DC_ERR_NO_CAMERA, DC_ERR_UNSUPPORTED, DC_ERR_NOMEM = -4, -5, -6
+
+EXPORTED_SYMBOLS = [
+    "dc_version", "dc_device_count", "dc_create", "dc_destroy", "dc_last_error",
+    "dc_set_pinhole", "dc_set_equirectangular", "dc_set_frame_size", "dc_width",
+    "dc_height", "dc_convert_device", "dc_convert_host", "dc_synchronize",
+    "dc_host_alloc", "dc_host_free", "dc_synth_depth_device", "dc_kernel_launches",
+]
+
+
+class DcJob(C.Structure):
+    _fields_ = [
+        ("feature", C.c_int32), ("in_kind", C.c_int32), ("out_kind", C.c_int32),
+        ("n_frames", C.c_int32), ("in_", C.c_void_p), ("out", C.c_void_p * 4),
+        ("clamp_lo", C.c_float), ("clamp_hi", C.c_float),
+        ("scale", C.c_double), ("offset", C.c_double),
+    ]
+
+
+class DcError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"depthconv_b200 error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def lib():
+    """Load libdepthconv_b200.so (raises if it has not been built)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FileNotFoundError(
+                f"{LIB_PATH} is missing: run `make -C {HERE}` "
+                "(__graft_entry__.build()); there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        L.dc_version.restype = C.c_char_p
+        L.dc_last_error.restype = C.c_char_p
+        L.dc_last_error.argtypes = [C.c_void_p]
+        L.dc_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+        L.dc_destroy.argtypes = [C.c_void_p]
+        L.dc_destroy.restype = None
+        L.dc_set_pinhole.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_float] * 4
+        L.dc_set_equirectangular.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float]
+        L.dc_set_frame_size.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.dc_width.argtypes = [C.c_void_p]
+        L.dc_height.argtypes = [C.c_void_p]
+        L.dc_convert_device.argtypes = [C.c_void_p, C.POINTER(DcJob), C.c_void_p]
+        L.dc_convert_host.argtypes = [C.c_void_p, C.POINTER(DcJob)]
+        L.dc_synchronize.argtypes = [C.c_void_p]
+        L.dc_host_alloc.restype = C.c_void_p
+        L.dc_host_alloc.argtypes = [C.c_size_t]
+        L.dc_host_free.argtypes = [C.c_void_p]
+        L.dc_host_free.restype = None
+        L.dc_synth_depth_device.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int,
+                                            C.c_void_p, C.c_void_p]
+        L.dc_kernel_launches.restype = C.c_uint64
+        L.dc_kernel_launches.argtypes = [C.c_void_p]
+        _lib = L
+    return _lib
+
+
+_IN_DTYPE = {DC_IN_U16_DEPTH: np.uint16, DC_IN_U16_RANGE: np.uint16, DC_IN_F32_RANGE: np.float32}
+_OUT_DTYPE = {DC_OUT_F32: np.float32, DC_OUT_U16: np.uint16}
+
+
+class Context:
+    """One context per (thread, GPU)."""
+
+    def __init__(self, device=0):
+        self._L = lib()
+        h = C.c_void_p()
+        rc = self._L.dc_create(device, C.byref(h))
+        if rc != DC_OK:
+            raise DcError(rc, self._L.dc_last_error(None).decode())
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.dc_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, rc):
+        if rc != DC_OK:
+            raise DcError(rc, self._L.dc_last_error(self._h).decode())
+
+    def status(self, rc):
+        return rc, self._L.dc_last_error(self._h).decode()
+
+    # -- camera ------------------------------------------------------------
+    def set_pinhole(self, w, h, fx, fy, cx, cy):
+        self._check(self._L.dc_set_pinhole(self._h, w, h, fx, fy, cx, cy))
+
+    def set_equirectangular(self, w, h, theta_min, theta_max):
+        self._check(self._L.dc_set_equirectangular(self._h, w, h, theta_min, theta_max))
+
+    def set_frame_size(self, w, h):
+        self._check(self._L.dc_set_frame_size(self._h, w, h))
+
+    @property
+    def size(self):
+        return self._L.dc_width(self._h), self._L.dc_height(self._h)
+
+    @property
+    def kernel_launches(self):
+        return int(self._L.dc_kernel_launches(self._h))
+
+    def synchronize(self):
+        self._check(self._L.dc_synchronize(self._h))
+
+    # -- raw calls -----------------------------------------------------------
+    def make_job(self, feature, in_kind, out_kind, n_frames, in_ptr, out_ptrs,
+                 clamp=(-20.0, 20.0), scale=1.0, offset=0.0):
+        j = DcJob()
+        j.feature, j.in_kind, j.out_kind, j.n_frames = feature, in_kind, out_kind, n_frames
+        j.in_ = in_ptr
+        for k in range(4):
+            j.out[k] = out_ptrs[k] if k < len(out_ptrs) and out_ptrs[k] else None
+        j.clamp_lo, j.clamp_hi = clamp
+        j.scale, j.offset = scale, offset
+        return j
+
+    def convert_device_raw(self, job, stream=None):
+        return self._L.dc_convert_device(self._h, C.byref(job), stream)
+
+    def convert_host_raw(self, job):
+        return self._L.dc_convert_host(self._h, C.byref(job))
+
+    def convert_device(self, job, stream=None):
+        self._check(self.convert_device_raw(job, stream))
+
+    # -- numpy convenience (host buffers) -----------------------------------
+    def convert(self, feature, frames, in_kind, out_kind=DC_OUT_F32, want=(True,),
+                clamp=(-20.0, 20.0), scale=1.0, offset=0.0):
+        """frames: (n, h, w) or (h, w) array of the in_kind dtype. `want[k]`
+        selects output slot k. Returns a list with an array (same leading shape)
+        per wanted slot, None for the others."""
+        frames = np.ascontiguousarray(frames, _IN_DTYPE[in_kind])
+        single = frames.ndim == 2
+        f3 = frames[None] if single else frames
+        n = f3.shape[0]
+        outs = [np.empty(f3.shape, _OUT_DTYPE[out_kind]) if (k < len(want) and want[k]) else None
+                for k in range(4)]
+        job = self.make_job(feature, in_kind, out_kind, n, f3.ctypes.data,
+                            [o.ctypes.data if o is not None else None for o in outs],
+                            clamp, scale, offset)
+        self._check(self.convert_host_raw(job))
+        return [(o[0] if single else o) if o is not None else None for o in outs]
+
+    def synth_depth_device(self, seed, frame0, n_frames, out_ptr, stream=None):
+        self._check(self._L.dc_synth_depth_device(self._h, seed, frame0, n_frames,
+                                                  out_ptr, stream))

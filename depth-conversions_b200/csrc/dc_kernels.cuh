@@ -1,0 +1,452 @@
+// Fused depth -> feature kernels for sm_100a.
+//
+// One launch converts a whole chunk of frames: grid = (column tiles, row tiles,
+// frames). A thread owns PX consecutive pixels of one image row (PX = 4 when
+// the width allows 8/16-byte vector access, else 1), reads the 3 x (PX + 2)
+// neighbourhood of the u16 / f32 input straight from global memory (the three
+// row reads of neighbouring threads hit L1/L2, HBM sees every input byte once),
+// converts orthographic depth to range in registers, evaluates the stencil and
+// writes PX quantised (or float) output pixels with one vector store per
+// output image. Camera-only constants come from per-intrinsic tables (or a
+// scalar when a table is uniform), never from per-pixel acosf/cosf/sqrt(double).
+#ifndef DC_KERNELS_CUH
+#define DC_KERNELS_CUH
+
+#include "dc_math.cuh"
+
+#include <cstdint>
+
+namespace dc {
+
+enum : int { IN_U16_DEPTH = 0, IN_U16_RANGE = 1, IN_F32_RANGE = 2 };
+enum : int { OUT_F32 = 0, OUT_U16 = 1 };
+enum : int {
+    FEAT_RANGE     = 0,
+    FEAT_BEARING   = 1,
+    FEAT_FLEXION   = 2,
+    FEAT_CURVATURE = 3,
+    FEAT_MAX_CURVE = 4,
+    FEAT_SCALE     = 5
+};
+
+// A per-pixel table or, when p == nullptr, one value for every pixel.
+struct tab_ref {
+    const float* p;
+    float        value;
+};
+
+struct kparams {
+    const void* in;
+    void*       out[4];
+    int         w, h;
+    long long   frame_px;  // w * h
+    tab_ref     range_factor;
+    const float *ray_x, *ray_y, *ray_z;
+    tab_ref     cosp[4];  // cos(phi(central, prior)): hor, ver, dia, anti
+    tab_ref     d_phi, d_theta, d_phi_theta;
+    float       lo, hi;       // curvature clamp (u16 output)
+    float       q_bearing;    // 65535 / pi
+    float       q_max_curve;  // 65535 / (2 pi)
+    float       s_scale, s_offset;  // FEAT_SCALE
+};
+
+// ---------------------------------------------------------------------------
+// row access
+template <int IN>
+struct in_elem {
+    using type = unsigned short;
+};
+template <>
+struct in_elem<IN_F32_RANGE> {
+    using type = float;
+};
+
+template <int PX>
+__device__ __forceinline__ void load_vec(const unsigned short* p, float (&o)[PX]) {
+    if constexpr (PX == 4) {
+        const uint2 r = __ldg(reinterpret_cast<const uint2*>(p));
+        o[0]          = float(r.x & 0xffffu);
+        o[1]          = float(r.x >> 16);
+        o[2]          = float(r.y & 0xffffu);
+        o[3]          = float(r.y >> 16);
+    } else {
+#pragma unroll
+        for (int i = 0; i < PX; ++i)
+            o[i] = float(__ldg(p + i));
+    }
+}
+template <int PX>
+__device__ __forceinline__ void load_vec(const float* p, float (&o)[PX]) {
+    if constexpr (PX == 4) {
+        const float4 r = __ldg(reinterpret_cast<const float4*>(p));
+        o[0] = r.x, o[1] = r.y, o[2] = r.z, o[3] = r.w;
+    } else {
+#pragma unroll
+        for (int i = 0; i < PX; ++i)
+            o[i] = __ldg(p + i);
+    }
+}
+__device__ __forceinline__ float load_one(const unsigned short* p) {
+    return float(__ldg(p));
+}
+__device__ __forceinline__ float load_one(const float* p) { return __ldg(p); }
+
+// Loads row `v` of `img`, columns u0-1 .. u0+PX, into o[0 .. PX+1]; pixels
+// outside the image read as 0 (never used by a computed pixel: the reference
+// leaves the border at 0 and skips it).
+template <int PX, bool LEFT, bool RIGHT, typename T>
+__device__ __forceinline__ void load_row(const T* img, int w, int h, int v, int u0,
+                                         float (&o)[PX + 2]) {
+    if (v < 0 || v >= h) {
+#pragma unroll
+        for (int i = 0; i < PX + 2; ++i)
+            o[i] = 0.0f;
+        return;
+    }
+    const T* row = img + size_t(v) * w;
+    float    c[PX];
+    load_vec<PX>(row + u0, c);
+#pragma unroll
+    for (int i = 0; i < PX; ++i)
+        o[i + 1] = c[i];
+    o[0]      = (LEFT && u0 > 0) ? load_one(row + u0 - 1) : 0.0f;
+    o[PX + 1] = (RIGHT && u0 + PX < w) ? load_one(row + u0 + PX) : 0.0f;
+}
+
+// table row access with the uniform shortcut
+template <int PX>
+__device__ __forceinline__ void load_tab(const tab_ref& t, int w, int v, int u0,
+                                         float (&o)[PX]) {
+    if (t.p == nullptr) {
+#pragma unroll
+        for (int i = 0; i < PX; ++i)
+            o[i] = t.value;
+    } else {
+        load_vec<PX>(t.p + size_t(v) * w + u0, o);
+    }
+}
+__device__ __forceinline__ float tab_at(const tab_ref& t, int w, int v, int u) {
+    return t.p == nullptr ? t.value : __ldg(t.p + size_t(v) * w + u);
+}
+
+// Range (Euclidean distance) of row v, columns u0-1..u0+PX.
+// IN_U16_DEPTH: conversion/util.h:41-51, float(d) * sqrtf(z_helper); d == 0
+// gives 0 * factor = 0, the value the reference returns early.
+template <int IN, int PX, bool LEFT, bool RIGHT>
+__device__ __forceinline__ void load_range_row(const kparams& p, const void* frame,
+                                               int v, int u0, float (&o)[PX + 2]) {
+    using T = typename in_elem<IN>::type;
+    load_row<PX, LEFT, RIGHT>(static_cast<const T*>(frame), p.w, p.h, v, u0, o);
+    if constexpr (IN == IN_U16_DEPTH) {
+        if (p.range_factor.p == nullptr) {
+#pragma unroll
+            for (int i = 0; i < PX + 2; ++i)
+                o[i] = mul(o[i], p.range_factor.value);
+        } else {
+            float f[PX + 2];
+            load_row<PX, LEFT, RIGHT>(p.range_factor.p, p.w, p.h, v, u0, f);
+#pragma unroll
+            for (int i = 0; i < PX + 2; ++i)
+                o[i] = mul(o[i], f[i]);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// stores
+template <int OUT>
+struct out_elem {
+    using type = float;
+};
+template <>
+struct out_elem<OUT_U16> {
+    using type = unsigned short;
+};
+
+template <int PX>
+__device__ __forceinline__ void store_vec(float* p, const float (&v)[PX]) {
+    if constexpr (PX == 4)
+        *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    else {
+#pragma unroll
+        for (int i = 0; i < PX; ++i)
+            p[i] = v[i];
+    }
+}
+template <int PX>
+__device__ __forceinline__ void store_vec(unsigned short* p,
+                                          const unsigned short (&v)[PX]) {
+    if constexpr (PX == 4)
+        *reinterpret_cast<uint2*>(p) = make_uint2(unsigned(v[0]) | (unsigned(v[1]) << 16),
+                                                  unsigned(v[2]) | (unsigned(v[3]) << 16));
+    else {
+#pragma unroll
+        for (int i = 0; i < PX; ++i)
+            p[i] = v[i];
+    }
+}
+
+// ---------------------------------------------------------------------------
+template <int FEAT, int IN, int OUT, int PX>
+__global__ void __launch_bounds__(256)
+    feature_kernel(const __grid_constant__ kparams p) {
+    using TI = typename in_elem<IN>::type;
+    using TO = typename out_elem<OUT>::type;
+
+    const int u0 = (blockIdx.x * blockDim.x + threadIdx.x) * PX;
+    const int v  = blockIdx.y * blockDim.y + threadIdx.y;
+    if (u0 >= p.w || v >= p.h)
+        return;
+    const size_t foff  = size_t(blockIdx.z) * size_t(p.frame_px);
+    const void*  frame = static_cast<const TI*>(p.in) + foff;
+    const size_t o0    = foff + size_t(v) * p.w + u0;
+    const int    w = p.w, h = p.h;
+    const bool   row_interior = (v >= 1) && (v < h - 1);
+
+    if constexpr (FEAT == FEAT_SCALE) {
+        // conversion/depth_scaling.h:21-31: saturate(round(d * scale + offset))
+        float c[PX];
+        load_vec<PX>(static_cast<const unsigned short*>(frame) + size_t(v) * w + u0, c);
+        unsigned short q[PX];
+#pragma unroll
+        for (int i = 0; i < PX; ++i)
+            q[i] = sat_u16_rn(add(mul(c[i], p.s_scale), p.s_offset));
+        store_vec<PX>(static_cast<unsigned short*>(p.out[0]) + o0, q);
+    } else if constexpr (FEAT == FEAT_RANGE) {
+        float r[PX + 2];
+        load_range_row<IN, PX, false, false>(p, frame, v, u0, r);
+        TO o[PX];
+#pragma unroll
+        for (int i = 0; i < PX; ++i) {
+            if constexpr (OUT == OUT_U16)
+                o[i] = sat_u16_rn(r[i + 1]);
+            else
+                o[i] = r[i + 1];
+        }
+        store_vec<PX>(static_cast<TO*>(p.out[0]) + o0, o);
+    } else if constexpr (FEAT == FEAT_BEARING) {
+        // conversion/depth_to_bearing.h:185-214; prior pixel per direction
+        // :96-114, computed region :135-178.
+        float up[PX + 2], mid[PX + 2], dn[PX + 2];
+        const bool want_up = p.out[1] != nullptr || p.out[2] != nullptr;
+        const bool want_dn = p.out[3] != nullptr;
+        if (want_up)
+            load_range_row<IN, PX, true, false>(p, frame, v - 1, u0, up);
+        load_range_row<IN, PX, true, false>(p, frame, v, u0, mid);
+        if (want_dn)
+            load_range_row<IN, PX, true, false>(p, frame, v + 1, u0, dn);
+#pragma unroll
+        for (int d = 0; d < 4; ++d) {
+            if (p.out[d] == nullptr)
+                continue;
+            float cs[PX];
+            load_tab<PX>(p.cosp[d], w, v, u0, cs);
+            TO o[PX];
+#pragma unroll
+            for (int i = 0; i < PX; ++i) {
+                const int  u = u0 + i;
+                float      prior;
+                bool       valid;
+                if (d == 0) {
+                    prior = mid[i];
+                    valid = u >= 1;
+                } else if (d == 1) {
+                    prior = up[i + 1];
+                    valid = v >= 1;
+                } else if (d == 2) {
+                    prior = up[i];
+                    valid = u >= 1 && v >= 1;
+                } else {
+                    prior = dn[i];
+                    valid = u >= 1 && v < h - 1;
+                }
+                const float a = valid ? bearing_pixel(mid[i + 1], prior, cs[i]) : 0.0f;
+                if constexpr (OUT == OUT_U16)
+                    o[i] = quant_scale(a, p.q_bearing);
+                else
+                    o[i] = a;
+            }
+            store_vec<PX>(static_cast<TO*>(p.out[d]) + o0, o);
+        }
+    } else {
+        // 3x3 stencils: interior pixels only, border stays 0
+        // (depth_to_flexion.h:156-161, depth_to_curvature.h:176-181,
+        //  depth_to_max_curve.h:101-102).
+        float up[PX + 2], mid[PX + 2], dn[PX + 2];
+        load_range_row<IN, PX, true, true>(p, frame, v - 1, u0, up);
+        load_range_row<IN, PX, true, true>(p, frame, v, u0, mid);
+        load_range_row<IN, PX, true, true>(p, frame, v + 1, u0, dn);
+
+        if constexpr (FEAT == FEAT_FLEXION) {
+            // to_camera(): P = d * ray for the 3 x (PX+2) window
+            vec3 P[3][PX + 2];
+            if (row_interior) {
+#pragma unroll
+                for (int r = 0; r < 3; ++r) {
+                    float rx[PX + 2], ry[PX + 2], rz[PX + 2];
+                    load_row<PX, true, true>(p.ray_x, w, h, v - 1 + r, u0, rx);
+                    load_row<PX, true, true>(p.ray_y, w, h, v - 1 + r, u0, ry);
+                    load_row<PX, true, true>(p.ray_z, w, h, v - 1 + r, u0, rz);
+                    const float* d = r == 0 ? up : (r == 1 ? mid : dn);
+#pragma unroll
+                    for (int i = 0; i < PX + 2; ++i)
+                        P[r][i] = {mul(d[i], rx[i]), mul(d[i], ry[i]), mul(d[i], rz[i])};
+                }
+            }
+            TO o[PX];
+#pragma unroll
+            for (int i = 0; i < PX; ++i) {
+                const int u = u0 + i;
+                float     f = 0.0f;
+                if (row_interior && u >= 1 && u < w - 1) {
+                    const int c = i + 1;
+                    f = flexion_from_points(P[0][c], P[2][c],          // (u,v-1) (u,v+1)
+                                            P[1][c - 1], P[1][c + 1],  // (u-1,v) (u+1,v)
+                                            P[0][c + 1], P[2][c - 1],  // (u+1,v-1) (u-1,v+1)
+                                            P[0][c - 1], P[2][c + 1]); // (u-1,v-1) (u+1,v+1)
+                }
+                if constexpr (OUT == OUT_U16)
+                    o[i] = quant_scale(f, 65535.0f);
+                else
+                    o[i] = f;
+            }
+            store_vec<PX>(static_cast<TO*>(p.out[0]) + o0, o);
+        } else if constexpr (FEAT == FEAT_CURVATURE) {
+            float a_phi[PX], a_theta[PX], a_pt[PX];
+            if (row_interior) {
+                load_tab<PX>(p.d_phi, w, v, u0, a_phi);
+                load_tab<PX>(p.d_theta, w, v, u0, a_theta);
+                load_tab<PX>(p.d_phi_theta, w, v, u0, a_pt);
+            }
+            TO g[PX], m[PX];
+#pragma unroll
+            for (int i = 0; i < PX; ++i) {
+                const int u = u0 + i, c = i + 1;
+                float     kg = 0.0f, km = 0.0f;
+                // DIFF_STAR, depth_to_curvature.h:97-115: any zero -> 0
+                const bool ok = row_interior && u >= 1 && u < w - 1 &&
+                                up[c - 1] != 0.0f && up[c] != 0.0f && up[c + 1] != 0.0f &&
+                                mid[c - 1] != 0.0f && mid[c] != 0.0f && mid[c + 1] != 0.0f &&
+                                dn[c - 1] != 0.0f && dn[c] != 0.0f && dn[c + 1] != 0.0f;
+                if (ok) {
+                    const derivs dv = derivatives(mid[c - 1], mid[c + 1], up[c], dn[c],
+                                                  mid[c], a_phi[i], a_theta[i], a_pt[i]);
+                    if (p.out[0] != nullptr)
+                        kg = gaussian_curvature(dv);
+                    if (p.out[1] != nullptr)
+                        km = mean_curvature(dv);
+                }
+                if constexpr (OUT == OUT_U16) {
+                    g[i] = quant_curvature(kg, mid[c], p.lo, p.hi);
+                    m[i] = quant_curvature(km, mid[c], p.lo, p.hi);
+                } else {
+                    g[i] = kg;
+                    m[i] = km;
+                }
+            }
+            if (p.out[0] != nullptr)
+                store_vec<PX>(static_cast<TO*>(p.out[0]) + o0, g);
+            if (p.out[1] != nullptr)
+                store_vec<PX>(static_cast<TO*>(p.out[1]) + o0, m);
+        } else if constexpr (FEAT == FEAT_MAX_CURVE) {
+            // depth_to_max_curve.h:113-139. Every phi() there is the angle
+            // between a pixel and one of its bearing "prior" neighbours, so the
+            // four cos_prior tables serve all eight angles:
+            //   hor1 = H(u,v)      hor2 = H(u+1,v)
+            //   ver1 = V(u,v)      ver2 = V(u,v+1)
+            //   dia1 = D(u,v)      dia2 = D(u+1,v+1)
+            //   ant1 = phi((u+1,v+1),(u,v)) = D(u+1,v+1)   (sic, :136)
+            //   ant2 = phi((u,v),(u+1,v-1)) = A(u+1,v-1)
+            float cH[PX + 1], cV0[PX], cV1[PX], cD0[PX], cD1[PX + 1], cA[PX + 1];
+            if (row_interior) {
+                load_tab<PX>(p.cosp[1], w, v, u0, cV0);
+                load_tab<PX>(p.cosp[1], w, v + 1, u0, cV1);
+                load_tab<PX>(p.cosp[2], w, v, u0, cD0);
+                float t[PX];
+                const bool more = u0 + PX < w;
+                load_tab<PX>(p.cosp[0], w, v, u0, t);
+#pragma unroll
+                for (int i = 0; i < PX; ++i)
+                    cH[i] = t[i];
+                cH[PX] = more ? tab_at(p.cosp[0], w, v, u0 + PX) : 0.0f;
+                load_tab<PX>(p.cosp[2], w, v + 1, u0, t);
+#pragma unroll
+                for (int i = 0; i < PX; ++i)
+                    cD1[i] = t[i];
+                cD1[PX] = more ? tab_at(p.cosp[2], w, v + 1, u0 + PX) : 0.0f;
+                load_tab<PX>(p.cosp[3], w, v - 1, u0, t);
+#pragma unroll
+                for (int i = 0; i < PX; ++i)
+                    cA[i] = t[i];
+                cA[PX] = more ? tab_at(p.cosp[3], w, v - 1, u0 + PX) : 0.0f;
+            }
+            TO o[PX];
+#pragma unroll
+            for (int i = 0; i < PX; ++i) {
+                const int u = u0 + i, c = i + 1;
+                float     a = 0.0f;
+                if (row_interior && u >= 1 && u < w - 1) {
+                    const float d0    = mid[c];
+                    const float a_hor = angle_formula(mid[c - 1], d0, mid[c + 1], cH[i], cH[i + 1]);
+                    const float a_ver = angle_formula(up[c], d0, dn[c], cV0[i], cV1[i]);
+                    const float a_dia = angle_formula(up[c - 1], d0, dn[c + 1], cD0[i], cD1[i + 1]);
+                    const float a_ant = angle_formula(dn[c - 1], d0, up[c + 1], cD1[i + 1], cA[i + 1]);
+                    a = fmaxf(a_hor, fmaxf(a_ver, fmaxf(a_dia, a_ant)));
+                }
+                if constexpr (OUT == OUT_U16)
+                    o[i] = quant_scale(a, p.q_max_curve);
+                else
+                    o[i] = a;
+            }
+            store_vec<PX>(static_cast<TO*>(p.out[0]) + o0, o);
+            if (p.out[1] != nullptr) {
+                // the fused `range` output (converter_laserscan.h.inl:9-10)
+                TO r[PX];
+#pragma unroll
+                for (int i = 0; i < PX; ++i) {
+                    if constexpr (OUT == OUT_U16)
+                        r[i] = sat_u16_rn(mid[i + 1]);
+                    else
+                        r[i] = mid[i + 1];
+                }
+                store_vec<PX>(static_cast<TO*>(p.out[1]) + o0, r);
+            }
+        }
+    }
+}
+
+// Synthetic depth generator (bench / test tooling), bit-identical to
+// oracle/dc_oracle.c dco_synth_depth.
+__device__ __forceinline__ unsigned long long splitmix64(unsigned long long x) {
+    unsigned long long z = x + 0x9E3779B97F4A7C15ull;
+    z                    = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z                    = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+__device__ __forceinline__ long long tri(long long t, long long p) {
+    const long long m = t % (2 * p);
+    return m < p ? p - m : m - p;
+}
+__global__ void __launch_bounds__(256)
+    synth_depth_kernel(unsigned long long seed, int frame0, int w, int h,
+                       unsigned short* out) {
+    const int u = blockIdx.x * blockDim.x + threadIdx.x;
+    const int v = blockIdx.y * blockDim.y + threadIdx.y;
+    if (u >= w || v >= h)
+        return;
+    const int                frame = frame0 + int(blockIdx.z);
+    const unsigned long long fkey  = (unsigned long long)frame * 0x9E3779B97F4A7C15ull;
+    const unsigned long long hsh =
+        splitmix64(seed ^ fkey ^ (unsigned long long)((long long)v * w + u));
+    long long d = 800 + 2 * tri((long long)u + 3ll * frame, 400) +
+                  3 * tri((long long)v + 5ll * frame, 300) + (long long)(hsh % 9) - 4;
+    const unsigned long long blk =
+        splitmix64(seed ^ (fkey + 0xD1B54A32D192ED03ull) ^
+                   (unsigned long long)(((long long)(v / 16)) * 4096 + (u / 16)));
+    if (blk % 100 < 25 || (hsh >> 32) % 100 < 5)
+        d = 0;
+    out[size_t(blockIdx.z) * size_t(w) * h + size_t(v) * w + u] = (unsigned short)d;
+}
+
+}  // namespace dc
+#endif

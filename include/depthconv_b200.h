@@ -1,0 +1,195 @@
+/* depthconv_b200 -- C ABI of the B200 (sm_100a) implementation of the
+ * depth-conversions hot path: depth map -> feature image stencil filters.
+ *
+ * This header is the drop-in boundary. Each entry point names the reference
+ * interface it replaces; paths are relative to the reference's src/ directory
+ * (JonasToth/depth-conversions). Plain pointers and sizes only: no C++ types,
+ * no torch types, no exceptions cross this boundary. INTEGRATION.md shows the
+ * binding a reference maintainer would add on top of it.
+ *
+ * Conventions
+ *   - Images are single channel, dense, row major: pixel (u, v) is data[v*w+u]
+ *     (include/sens_loc/math/image.h:95-108). Frames of a batch lie back to
+ *     back: frame f starts at element f*w*h.
+ *   - Every function returns a dc_status (0 = ok, < 0 = error) unless stated
+ *     otherwise; dc_last_error() gives the message for the last failure of a
+ *     context. CUDA errors are sticky per context.
+ *   - A context is bound to one GPU and is not re-entrant; use one context per
+ *     (host thread, GPU). Distinct contexts are independent.
+ *   - There is no CPU fallback: every conversion runs in the CUDA kernels of
+ *     this library or fails with an error.
+ */
+#ifndef DEPTHCONV_B200_H
+#define DEPTHCONV_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct dc_ctx dc_ctx;
+
+typedef enum dc_status {
+    DC_OK              = 0,
+    DC_ERR_INVALID     = -1, /* bad argument (null pointer, unknown enum, ...) */
+    DC_ERR_NO_DEVICE   = -2, /* no usable CUDA device / device index out of range */
+    DC_ERR_CUDA        = -3, /* a CUDA call or kernel failed (sticky) */
+    DC_ERR_NO_CAMERA   = -4, /* conversion requested before dc_set_* */
+    DC_ERR_UNSUPPORTED = -5, /* combination not provided by the reference either */
+    DC_ERR_NOMEM       = -6
+} dc_status;
+
+/* What to compute. One job = one fused kernel launch per chunk of frames. */
+typedef enum dc_feature {
+    /* conversion::depth_to_laserscan<float, ushort>
+     *   include/sens_loc/conversion/depth_to_laserscan.h:70-93
+     * and the `depth2x range` converter, apps/depth2x/converter_laserscan.h.inl:1-15.
+     *   out[0] = range image */
+    DC_RANGE = 0,
+    /* conversion::depth_to_bearing<direction>
+     *   include/sens_loc/conversion/depth_to_bearing.h:221-248
+     * and `depth2x bearing`, apps/depth2x/converter_bearing.h.inl:1-29 (which
+     * makes up to four full passes; here all requested directions come out of
+     * one pass over the input).
+     *   out[0] horizontal, out[1] vertical, out[2] diagonal, out[3] antidiagonal;
+     *   NULL = direction not wanted, at least one must be given */
+    DC_BEARING = 1,
+    /* conversion::depth_to_flexion
+     *   include/sens_loc/conversion/depth_to_flexion.h:147-167
+     * and `depth2x flexion`, apps/depth2x/converter_flexion.h.inl:1-12.
+     *   out[0] = flexion image */
+    DC_FLEXION = 2,
+    /* conversion::depth_to_gaussian_curvature / depth_to_mean_curvature
+     *   include/sens_loc/conversion/depth_to_curvature.h:166-206
+     * and `depth2x gauss-curvature|mean-curvature`,
+     * apps/depth2x/converter_curvature.h.inl:1-30.
+     *   out[0] = Gaussian curvature, out[1] = mean curvature (either may be NULL) */
+    DC_CURVATURE = 3,
+    /* conversion::depth_to_max_curve
+     *   include/sens_loc/conversion/depth_to_max_curve.h:86-153
+     * and `depth2x max-curve`, apps/depth2x/converter_max_curve.h.inl:1-13.
+     *   out[0] = max-curve image; out[1] (optional) = the range image of the
+     *   same pass, i.e. `depth2x range` fused in (BASELINE config 4) */
+    DC_MAX_CURVE = 4,
+    /* conversion::depth_scaling
+     *   include/sens_loc/conversion/depth_scaling.h:21-31
+     * and `depth2x scale`, apps/depth2x/converter_scale.cpp:9-19.
+     * Needs no camera. in_kind must be DC_IN_U16_RANGE, out_kind DC_OUT_U16.
+     *   out[0] = saturate(round(depth * scale + offset)) */
+    DC_SCALE = 5
+} dc_feature;
+
+/* What the input pixels are (apps/util/batch_converter.h:24-30 depth_type and
+ * the element type of math::image). */
+typedef enum dc_in_kind {
+    DC_IN_U16_DEPTH = 0, /* --type pinhole-depth: orthographic u16, converted to
+                            range first (batch_converter.h:157-159) */
+    DC_IN_U16_RANGE = 1, /* --type pinhole-range: Euclidean u16, widened to
+                            float (batch_converter.h:160) */
+    DC_IN_F32_RANGE = 2  /* math::image<float> range image: the argument type of
+                            the conversion::depth_to_* library functions */
+} dc_in_kind;
+
+/* What the output pixels are. */
+typedef enum dc_out_kind {
+    DC_OUT_F32 = 0, /* the float feature image the library functions return */
+    DC_OUT_U16 = 1  /* the 16 bit image depth2x writes: convert_bearing<float,
+                       ushort> (depth_to_bearing.h:282-301), convert_flexion
+                       <ushort> (depth_to_flexion.h:194-215), convert_max_curve
+                       <ushort> (depth_to_max_curve.h:156-176), curvature_to_image
+                       <ushort> with both clamps (depth_to_curvature.h:253-283),
+                       convertTo(CV_16U) for range (converter_laserscan.h.inl:9-10) */
+} dc_out_kind;
+
+#define DC_MAX_OUTPUTS 4
+
+typedef struct dc_job {
+    int32_t     feature;  /* dc_feature */
+    int32_t     in_kind;  /* dc_in_kind */
+    int32_t     out_kind; /* dc_out_kind */
+    int32_t     n_frames; /* frames in `in` and in every non-NULL out[] */
+    const void* in;       /* n_frames * w * h elements of the in_kind type */
+    void*       out[DC_MAX_OUTPUTS]; /* per-feature slots, see dc_feature */
+    float       clamp_lo; /* curvature, DC_OUT_U16: --lower-bound (default -20) */
+    float       clamp_hi; /* curvature, DC_OUT_U16: --upper-bound (default +20) */
+    double      scale;    /* DC_SCALE: --factor */
+    double      offset;   /* DC_SCALE: --delta */
+} dc_job;
+
+/* Library / device discovery. */
+const char* dc_version(void);
+int         dc_device_count(void); /* >= 0, or a negative dc_status */
+
+/* Create / destroy a context on GPU `device`. Owns all device memory, streams
+ * and pinned staging buffers it uses. */
+int  dc_create(int device, dc_ctx** ctx);
+void dc_destroy(dc_ctx* ctx);
+
+/* Message of the last error on this context ("" if none). Never NULL. With a
+ * NULL ctx: the message of the last failed dc_create on this thread. */
+const char* dc_last_error(const dc_ctx* ctx);
+
+/* Install the camera model; replaces the construction of
+ * camera_models::pinhole<float>(w, h, fx, fy, cx, cy)
+ *   include/sens_loc/camera_models/pinhole.h:26-50
+ * and hoists everything that depends on the camera only out of the per-frame
+ * path: unit rays (pinhole.h:142-171), the orthographic->range factor
+ * (conversion/util.h:41-51) and the ray angles phi() and their cosines
+ * (camera_models/utility.h:15-49) are computed once, with the host's libm, and
+ * kept in device tables. Same preconditions as the reference constructor
+ * (w, h > 0; fx, fy, cx, cy > 0): violated -> DC_ERR_INVALID. */
+int dc_set_pinhole(dc_ctx* ctx, int w, int h, float fx, float fy, float cx, float cy);
+
+/* camera_models::equirectangular<float>(w, h, {theta_min, theta_max})
+ *   include/sens_loc/camera_models/equirectangular.h:43-153
+ * (`depth2x -m equirectangular`). For this model the range conversion is the
+ * identity (conversion/util.h:57-67). */
+int dc_set_equirectangular(dc_ctx* ctx, int w, int h, float theta_min, float theta_max);
+
+/* Frame size only, no camera model: all that DC_SCALE needs (`depth2x scale`
+ * takes no --calibration; apps/depth2x/main.cpp:338-352). Clears any camera. */
+int dc_set_frame_size(dc_ctx* ctx, int w, int h);
+
+/* Size of the installed camera / frame size (0 if none). */
+int dc_width(const dc_ctx* ctx);
+int dc_height(const dc_ctx* ctx);
+
+/* Run a job whose `in` and `out[]` pointers are DEVICE memory on this
+ * context's GPU. Asynchronous: enqueued on `cuda_stream` (a cudaStream_t /
+ * CUstream, NULL = the context's own stream); returns after the launch.
+ * Buffers must stay valid until the stream reaches this point. */
+int dc_convert_device(dc_ctx* ctx, const dc_job* job, void* cuda_stream);
+
+/* Run a job whose `in` and `out[]` pointers are HOST memory. Synchronous: on
+ * return all outputs are written. Frames are processed in chunks through a
+ * double-buffered H2D -> kernel -> D2H pipeline on the context's streams.
+ * Pinned memory (dc_host_alloc, cudaHostAlloc, torch pin_memory) is copied
+ * straight by DMA; pageable memory is staged through the context's pinned ring.
+ * This is the call the conversion::depth_to_* drop-in wrappers and the depth2x
+ * frame pipeline make. */
+int dc_convert_host(dc_ctx* ctx, const dc_job* job);
+
+/* Block until all work this context enqueued on its own streams has finished. */
+int dc_synchronize(dc_ctx* ctx);
+
+/* Pinned host memory for zero-staging dc_convert_host calls. */
+void* dc_host_alloc(size_t bytes);
+void  dc_host_free(void* p);
+
+/* Synthetic Kinect-like orthographic depth frames (DESIGN.md "Synthetic
+ * input"), generated on the device: frames [frame0, frame0 + n_frames) of the
+ * stream identified by `seed`, w x h taken from the installed camera.
+ * Benchmark / test tooling; bit-identical to oracle/dc_oracle.c dco_synth_depth. */
+int dc_synth_depth_device(dc_ctx* ctx, uint64_t seed, int frame0, int n_frames,
+                          uint16_t* out_device, void* cuda_stream);
+
+/* Number of kernels of this library launched on this context since creation
+ * (for the benchmark's gpu_launches claim). */
+uint64_t dc_kernel_launches(const dc_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DEPTHCONV_B200_H */

@@ -363,8 +363,15 @@ void dco_max_curve(const float* range, const dco_pinhole* k, float* out) {
 /* Quantisers. cv::Mat::convertTo(dst, CV_16U, alpha, beta) on a 32F source is
  * saturate_cast<ushort>(src * (float)alpha + (float)beta): cvRound (round half
  * to even) then clamp to [0, 65535]. */
+static long cv_round(float v) {
+    /* OpenCV cvRound(float) is cvtss2si to a 32 bit int: NaN and anything
+     * outside the int range become INT_MIN ("integer indefinite"). */
+    if (!(fabsf(v) < 2147483648.0f))
+        return -2147483647L - 1L;
+    return lrintf(v);
+}
 static uint16_t sat_u16(float v) {
-    const long r = lrintf(v); /* NaN/huge -> LONG_MIN on x86-64 -> clamps to 0 */
+    const long r = cv_round(v);
     return (uint16_t)(r < 0 ? 0 : (r > 65535 ? 65535 : r));
 }
 static void convert_scale_u16(const float* in, size_t n, float alpha, float beta,
@@ -414,7 +421,7 @@ void dco_curvature_to_image_u16(const float* curv, const float* range, size_t n,
          * NaN -> 0x80000000 -> 0 */
         const uint16_t q = (uint16_t)(int)tc;
         /* mask: saturate_cast<uchar>(range) != 0 */
-        const long     m  = lrintf(range[i]);
+        const long     m  = cv_round(range[i]);
         const int      on = (m < 0 ? 0 : (m > 255 ? 255 : m)) != 0;
         out[i]            = on ? q : 0;
     }

@@ -69,10 +69,12 @@ inline D saturate_round(W v) {
     if constexpr (std::is_floating_point_v<D>) {
         return static_cast<D>(v);
     } else {
-        // lrint with the default rounding mode is round-half-to-even.
-        // NaN/huge values: the x86 conversion returns LONG_MIN, which clamps
-        // to the minimum of the destination type.
-        const long r  = std::lrint(v);
+        // cvRound: lrint with the default rounding mode is round-half-to-even;
+        // it converts to a 32 bit int (cvtss2si / cvtsd2si), so NaN and values
+        // outside the int range become INT_MIN, which then clamps to the
+        // minimum of the destination type.
+        const long r = (std::fabs(v) < W(2147483648.0)) ? std::lrint(v)
+                                                        : (-2147483647L - 1L);
         const long lo = static_cast<long>(std::numeric_limits<D>::min());
         const long hi = static_cast<long>(std::numeric_limits<D>::max());
         return static_cast<D>(r < lo ? lo : (r > hi ? hi : r));

@@ -1,0 +1,176 @@
+"""GPU: the CUDA path, called through the C ABI, against the oracle and the
+committed golden vectors. Tolerances: parity.py."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from oracle_lib import (F_BEARING_H, F_FLEXION, F_GAUSS, F_MAX_CURVE, F_MEAN,
+                        FEATURE_NAMES, kinect_scaled)
+from parity import assert_float_parity, assert_u16_parity
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+CASES = sorted(os.path.basename(p) for p in glob.glob(os.path.join(GOLD, "*x*.npz")))
+
+
+def set_k(ctx, k):
+    ctx.set_pinhole(k["w"], k["h"], k["fx"], k["fy"], k["cx"], k["cy"])
+
+
+def gpu_all_features(pkg, ctx, frames, in_kind, out_kind, clamp=(-20.0, 20.0)):
+    """Every feature image of the hot path for `frames`, keyed like the goldens."""
+    P = pkg
+    res = {}
+    res["range"] = ctx.convert(P.DC_RANGE, frames, in_kind, out_kind)[0]
+    b = ctx.convert(P.DC_BEARING, frames, in_kind, out_kind, want=(True,) * 4)
+    res["bearing_h"], res["bearing_v"], res["bearing_d"], res["bearing_a"] = b
+    res["flexion"] = ctx.convert(P.DC_FLEXION, frames, in_kind, out_kind)[0]
+    res["gauss"], res["mean"] = ctx.convert(P.DC_CURVATURE, frames, in_kind, out_kind,
+                                            want=(True, True), clamp=clamp)[:2]
+    mc = ctx.convert(P.DC_MAX_CURVE, frames, in_kind, out_kind, want=(True, True))
+    res["max_curve"], res["range_fused"] = mc[0], mc[1]
+    return res
+
+
+def intr(z):
+    w, h, fx, fy, cx, cy = z["intrinsic"]
+    return dict(w=int(w), h=int(h), fx=float(fx), fy=float(fy), cx=float(cx), cy=float(cy))
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_golden_vectors(pkg, gpu_ctx, case):
+    z = np.load(os.path.join(GOLD, case))
+    k, depth = intr(z), z["depth"]
+    set_k(gpu_ctx, k)
+    for kind, in_kind in ((0, pkg.DC_IN_U16_DEPTH), (1, pkg.DC_IN_U16_RANGE)):
+        if f"k{kind}_range" not in z:
+            continue
+        f32 = gpu_all_features(pkg, gpu_ctx, depth, in_kind, pkg.DC_OUT_F32)
+        u16 = gpu_all_features(pkg, gpu_ctx, depth, in_kind, pkg.DC_OUT_U16)
+        for n in FEATURE_NAMES.values():
+            assert_float_parity(n, f32[n], z[f"k{kind}_{n}"])
+            assert_u16_parity(n, u16[n], z[f"k{kind}_{n}_u16"])
+        assert_float_parity("range", f32["range_fused"], z[f"k{kind}_range"])
+        assert_u16_parity("range", u16["range_fused"], z[f"k{kind}_range_u16"])
+        # library API: float range image in (math::image<float>)
+        lib = gpu_all_features(pkg, gpu_ctx, z[f"k{kind}_range"], pkg.DC_IN_F32_RANGE,
+                               pkg.DC_OUT_F32)
+        for n in FEATURE_NAMES.values():
+            assert_float_parity(n, lib[n], z[f"k{kind}_{n}"])
+
+
+@pytest.mark.parametrize("w,h", [(960, 540), (480, 270), (322, 203)])
+def test_batch_against_oracle(pkg, gpu_ctx, oracle, w, h):
+    """A batch of synthetic frames (BASELINE config 1/2 size and the 480x270 /
+    ragged-width cases), every feature, both output types."""
+    k = kinect_scaled(w, h)
+    set_k(gpu_ctx, k)
+    n = 3
+    frames = np.stack([oracle.synth_depth(0xD2C00001, f, w, h) for f in range(n)])
+    f32 = gpu_all_features(pkg, gpu_ctx, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_F32)
+    u16 = gpu_all_features(pkg, gpu_ctx, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16,
+                           clamp=(-5.0, 11.0))
+    stats = {}
+    for i in range(n):
+        rng = oracle.laserscan(frames[i], k)
+        for f, name in FEATURE_NAMES.items():
+            want = oracle.feature(f, rng, k)
+            eq = assert_float_parity(name, f32[name][i], want)
+            stats[name] = min(stats.get(name, 1.0), eq)
+            assert_u16_parity(name, u16[name][i], oracle.quantise(f, want, rng, -5.0, 11.0))
+    print("bit-equal fraction per feature:", {k_: round(v, 6) for k_, v in stats.items()})
+    assert stats["mean"] > 0.99
+
+
+def test_single_outputs_and_direction_subsets(pkg, gpu_ctx, oracle):
+    """bearing with only some directions / curvature with one output: the other
+    slots stay untouched (converter_bearing.h.inl:13-26)."""
+    w, h = 160, 96
+    k = kinect_scaled(w, h)
+    set_k(gpu_ctx, k)
+    d = oracle.synth_depth(0xD2C00005, 0, w, h)
+    rng = oracle.laserscan(d, k)
+    for want in [(True, False, False, False), (False, False, False, True),
+                 (False, True, True, False)]:
+        outs = gpu_ctx.convert(pkg.DC_BEARING, d, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_F32, want=want)
+        for i, on in enumerate(want):
+            assert (outs[i] is not None) == on
+            if on:
+                assert_float_parity("bearing", outs[i], oracle.feature(F_BEARING_H + i, rng, k))
+    g, m = gpu_ctx.convert(pkg.DC_CURVATURE, d, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_F32,
+                           want=(True, False))[:2]
+    assert m is None
+    assert_float_parity("gauss", g, oracle.feature(F_GAUSS, rng, k))
+    g, m = gpu_ctx.convert(pkg.DC_CURVATURE, d, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_F32,
+                           want=(False, True))[:2]
+    assert g is None
+    assert_float_parity("mean", m, oracle.feature(F_MEAN, rng, k))
+
+
+def test_edge_inputs(pkg, gpu_ctx, oracle):
+    """all-invalid frame, all-valid flat frame, maximum depth, single zero."""
+    w, h = 64, 48
+    k = kinect_scaled(w, h)
+    set_k(gpu_ctx, k)
+    frames = np.zeros((4, h, w), np.uint16)
+    frames[1] = 1500
+    frames[2] = 65535
+    frames[3] = 1000
+    frames[3, 20, 30] = 0
+    f32 = gpu_all_features(pkg, gpu_ctx, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_F32)
+    u16 = gpu_all_features(pkg, gpu_ctx, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)
+    for i in range(4):
+        rng = oracle.laserscan(frames[i], k)
+        for f, name in FEATURE_NAMES.items():
+            want = oracle.feature(f, rng, k)
+            assert_float_parity(name, f32[name][i], want)
+            assert_u16_parity(name, u16[name][i], oracle.quantise(f, want, rng))
+    assert not f32["flexion"][0].any() and not f32["max_curve"][0].any()
+    # empty batch is a no-op
+    job = gpu_ctx.make_job(pkg.DC_FLEXION, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16, 0,
+                           frames.ctypes.data, [frames.ctypes.data])
+    assert gpu_ctx.convert_host_raw(job) == pkg.DC_OK
+
+
+def test_scale_and_pinhole_range_roundtrip(pkg, gpu_ctx, oracle):
+    """depth2x scale (test_conversion_scaling.cpp:13-39: x8 saturates, +10000
+    offset) and range -> `--type pinhole-range` flexion (test_depth2x_range.sh:58-76)."""
+    w, h = 96, 64
+    k = kinect_scaled(w, h)
+    d = oracle.synth_depth(0xD2C00006, 0, w, h)
+    d[3, 3] = 60000
+    gpu_ctx.set_frame_size(w, h)
+    for s, o in ((8.0, 0.0), (1.0, 10000.0), (0.37, -12.5)):
+        got = gpu_ctx.convert(pkg.DC_SCALE, d, pkg.DC_IN_U16_RANGE, pkg.DC_OUT_U16,
+                              scale=s, offset=o)[0]
+        assert np.array_equal(got, oracle.depth_scaling(d, s, o))
+    job = gpu_ctx.make_job(pkg.DC_FLEXION, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16, 1,
+                           d.ctypes.data, [d.ctypes.data])
+    assert gpu_ctx.convert_host_raw(job) == pkg.DC_ERR_NO_CAMERA
+    set_k(gpu_ctx, k)
+    rng_u16 = gpu_ctx.convert(pkg.DC_RANGE, d, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)[0]
+    fl = gpu_ctx.convert(pkg.DC_FLEXION, rng_u16, pkg.DC_IN_U16_RANGE, pkg.DC_OUT_U16)[0]
+    _, _, want = oracle.cli_frame(F_FLEXION, 1, rng_u16, k)
+    assert np.array_equal(fl, want)
+
+
+def test_bad_jobs_are_rejected(pkg, gpu_ctx):
+    P = pkg
+    k = kinect_scaled(32, 16)
+    set_k(gpu_ctx, k)
+    buf = np.zeros((16, 32), np.uint16)
+    p = buf.ctypes.data
+    J = gpu_ctx.make_job
+    assert gpu_ctx.convert_host_raw(J(P.DC_BEARING, 0, 1, 1, p, [])) == P.DC_ERR_INVALID
+    assert gpu_ctx.convert_host_raw(J(99, 0, 1, 1, p, [p])) == P.DC_ERR_INVALID
+    assert gpu_ctx.convert_host_raw(J(P.DC_FLEXION, 0, 1, 1, None, [p])) == P.DC_ERR_INVALID
+    assert gpu_ctx.convert_host_raw(J(P.DC_SCALE, 0, 1, 1, p, [p])) == P.DC_ERR_UNSUPPORTED
+    assert gpu_ctx.convert_host_raw(J(P.DC_CURVATURE, 0, 1, 1, p, [p], clamp=(3.0, 3.0))) \
+        == P.DC_ERR_INVALID
+    L = pkg.lib()
+    assert L.dc_set_pinhole(gpu_ctx._h, 0, 16, 1.0, 1.0, 1.0, 1.0) == P.DC_ERR_INVALID
+    assert L.dc_set_pinhole(gpu_ctx._h, 32, 16, 1.0, -1.0, 1.0, 1.0) == P.DC_ERR_INVALID
+    assert b"pinhole" in L.dc_last_error(gpu_ctx._h)
+    assert gpu_ctx.size == (32, 16)
