@@ -281,17 +281,34 @@ int ref_cli_frame_equi(int f, const uint16_t* depth, int w, int h,
 // directions = four ids, as converter_bearing.h.inl does four full passes).
 // outs_u16[k] receives n_frames images for features[k] (may be NULL entries).
 // threads <= 0: tf::Executor default (hardware_concurrency), as the CLI does.
+// n_distinct: number of frames actually present in `depth`; frame idx reads
+// depth[idx % n_distinct] (lets the timed baseline run many frames from a small
+// buffer). Outputs, when requested, must still hold n_frames images.
+int ref_cli_batch_cyclic(const int* features, int n_features, int in_kind,
+                         const uint16_t* depth, int n_distinct, int n_frames, int w,
+                         int h, float fx, float fy, float cx, float cy, double lo,
+                         double hi, uint16_t** outs_u16, int threads);
+
 int ref_cli_batch(const int* features, int n_features, int in_kind,
                   const uint16_t* depth, int n_frames, int w, int h, float fx,
                   float fy, float cx, float cy, double lo, double hi,
                   uint16_t** outs_u16, int threads) {
+    return ref_cli_batch_cyclic(features, n_features, in_kind, depth, n_frames,
+                                n_frames, w, h, fx, fy, cx, cy, lo, hi, outs_u16,
+                                threads);
+}
+
+int ref_cli_batch_cyclic(const int* features, int n_features, int in_kind,
+                         const uint16_t* depth, int n_distinct, int n_frames, int w,
+                         int h, float fx, float fy, float cx, float cy, double lo,
+                         double hi, uint16_t** outs_u16, int threads) {
     const pinhole<float> K(w, h, fx, fy, cx, cy);
     const std::size_t    px = std::size_t(w) * std::size_t(h);
     tf::Executor executor(threads > 0 ? unsigned(threads)
                                       : std::thread::hardware_concurrency());
     tf::Taskflow flow;
     flow.parallel_for(0, n_frames, 1, [&](int idx) {
-        const auto in16 = wrap<ushort>(depth + px * idx, w, h);
+        const auto in16 = wrap<ushort>(depth + px * (idx % n_distinct), w, h);
         const math::image<float> range =
             in_kind == 0 ? conversion::depth_to_laserscan<float, ushort>(in16, K)
                          : math::convert<float>(in16);

@@ -213,6 +213,9 @@ class RefLib:
         L.ref_cli_batch.argtypes = ([C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int,
                                      C.c_int, C.c_int] + f4 +
                                     [C.c_double, C.c_double, C.c_void_p, C.c_int])
+        L.ref_cli_batch_cyclic.argtypes = ([C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int,
+                                            C.c_int, C.c_int, C.c_int] + f4 +
+                                           [C.c_double, C.c_double, C.c_void_p, C.c_int])
 
     @staticmethod
     def _k(k):
@@ -278,10 +281,18 @@ class RefLib:
         return feat, q
 
     def cli_batch(self, features, in_kind, frames_u16, k, lo=-20.0, hi=20.0,
-                  threads=0, want_outputs=True):
-        """frames_u16: (n, h, w). Returns (list of (n,h,w) u16 arrays, workers)."""
+                  threads=0, want_outputs=True, n_frames=None):
+        """frames_u16: (n, h, w). Returns (list of (n,h,w) u16 arrays, workers).
+        n_frames > n re-reads the buffer cyclically (timed baseline; no outputs)."""
         frames_u16 = np.ascontiguousarray(frames_u16)
         n = frames_u16.shape[0]
+        if n_frames is not None and n_frames != n:
+            assert not want_outputs
+            feats = (C.c_int * len(features))(*features)
+            workers = self.lib.ref_cli_batch_cyclic(
+                C.cast(feats, C.c_void_p), len(features), in_kind, _ptr(frames_u16), n,
+                n_frames, *self._k(k), lo, hi, None, threads)
+            return [], workers
         feats = (C.c_int * len(features))(*features)
         outs = [np.empty(frames_u16.shape, np.uint16) for _ in features] if want_outputs else []
         if want_outputs:
