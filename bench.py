@@ -92,10 +92,10 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.samples, self._stop = index, [], threading.Event()
+        self.index, self.samples, self._halt = index, [], threading.Event()
 
     def run(self):
-        while not self._stop.is_set():
+        while not self._halt.is_set():
             try:
                 out = subprocess.run(
                     ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
@@ -105,10 +105,10 @@ class ClockSampler(threading.Thread):
                     self.samples.append(parts)
             except Exception:
                 pass
-            self._stop.wait(0.05)
+            self._halt.wait(0.05)
 
     def stop(self):
-        self._stop.set()
+        self._halt.set()
         self.join(timeout=6)
         sm = [float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit()]
         mx = [float(s[1]) for s in self.samples if s[1].replace(".", "").isdigit()]
@@ -216,7 +216,11 @@ def run_ours(args, wl):
 
     ctx = pkg.Context(local)
     ctx.set_pinhole(w, h, k["fx"], k["fy"], k["cx"], k["cy"])
-    stream = torch.cuda.current_stream()
+    # A real (non-NULL) stream: NULL would select the context's own stream and
+    # the CUDA events below would not bracket the kernels.
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     sptr = ctypes.c_void_p(stream.cuda_stream)
 
     # frames sharded by frame index: rank r owns frames [r*F, (r+1)*F) of every step
