@@ -237,7 +237,7 @@ int validate_job(dc_ctx* c, const dc_job* j) {
 
 // ---------------------------------------------------------------------------
 template <int FEAT, int IN, int OUT>
-cudaError_t launch_px(const dc::kparams& p, int n_frames, cudaStream_t s, bool vec4) {
+cudaError_t launch_px(const dc::kparams& p, int n_frames, cudaStream_t s, bool vec4, bool fast) {
     const int px = vec4 ? 4 : 1;
     const int qw = (p.w + px - 1) / px;
     // pick the block shape that wastes the fewest threads
@@ -264,10 +264,12 @@ cudaError_t launch_px(const dc::kparams& p, int n_frames, cudaStream_t s, bool v
             if (p.out[k] != nullptr)
                 q.out[k] = static_cast<char*>(p.out[k]) + size_t(f0) * p.frame_px * out_b;
         const dim3 grid(gx, gy, unsigned(nf));
-        if (vec4)
-            dc::feature_kernel<FEAT, IN, OUT, 4><<<grid, block, 0, s>>>(q);
+        if (vec4 && fast)
+            dc::feature_kernel<FEAT, IN, OUT, 4, true><<<grid, block, 0, s>>>(q);
+        else if (vec4)
+            dc::feature_kernel<FEAT, IN, OUT, 4, false><<<grid, block, 0, s>>>(q);
         else
-            dc::feature_kernel<FEAT, IN, OUT, 1><<<grid, block, 0, s>>>(q);
+            dc::feature_kernel<FEAT, IN, OUT, 1, false><<<grid, block, 0, s>>>(q);
         const cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess)
             return e;
@@ -276,17 +278,18 @@ cudaError_t launch_px(const dc::kparams& p, int n_frames, cudaStream_t s, bool v
 }
 
 template <int FEAT, int IN>
-cudaError_t launch_out(const dc::kparams& p, int out_kind, int n, cudaStream_t s, bool v4) {
-    return out_kind == DC_OUT_F32 ? launch_px<FEAT, IN, dc::OUT_F32>(p, n, s, v4)
-                                  : launch_px<FEAT, IN, dc::OUT_U16>(p, n, s, v4);
+cudaError_t launch_out(const dc::kparams& p, int out_kind, int n, cudaStream_t s, bool v4,
+                       bool fast) {
+    return out_kind == DC_OUT_F32 ? launch_px<FEAT, IN, dc::OUT_F32>(p, n, s, v4, fast)
+                                  : launch_px<FEAT, IN, dc::OUT_U16>(p, n, s, v4, fast);
 }
 template <int FEAT>
 cudaError_t launch_in(const dc::kparams& p, int in_kind, int out_kind, int n, cudaStream_t s,
-                      bool v4) {
+                      bool v4, bool fast) {
     switch (in_kind) {
-    case DC_IN_U16_DEPTH: return launch_out<FEAT, dc::IN_U16_DEPTH>(p, out_kind, n, s, v4);
-    case DC_IN_U16_RANGE: return launch_out<FEAT, dc::IN_U16_RANGE>(p, out_kind, n, s, v4);
-    default: return launch_out<FEAT, dc::IN_F32_RANGE>(p, out_kind, n, s, v4);
+    case DC_IN_U16_DEPTH: return launch_out<FEAT, dc::IN_U16_DEPTH>(p, out_kind, n, s, v4, fast);
+    case DC_IN_U16_RANGE: return launch_out<FEAT, dc::IN_U16_RANGE>(p, out_kind, n, s, v4, fast);
+    default: return launch_out<FEAT, dc::IN_F32_RANGE>(p, out_kind, n, s, v4, false);
     }
 }
 
@@ -343,15 +346,17 @@ int launch_job(dc_ctx* c, const dc_job* j, cudaStream_t s) {
         if (j->out[k] != nullptr)
             v4 = v4 && aligned(j->out[k], j->out_kind == DC_OUT_F32 ? 16 : 8);
 
+    // guard-free exact arithmetic needs the per-camera range proof (dc_tables)
+    const bool fast = c->tabs.fast_ok;
     cudaError_t e = cudaSuccess;
     switch (j->feature) {
-    case DC_RANGE: e = launch_in<dc::FEAT_RANGE>(p, in_kind, j->out_kind, j->n_frames, s, v4); break;
-    case DC_BEARING: e = launch_in<dc::FEAT_BEARING>(p, in_kind, j->out_kind, j->n_frames, s, v4); break;
-    case DC_FLEXION: e = launch_in<dc::FEAT_FLEXION>(p, in_kind, j->out_kind, j->n_frames, s, v4); break;
-    case DC_CURVATURE: e = launch_in<dc::FEAT_CURVATURE>(p, in_kind, j->out_kind, j->n_frames, s, v4); break;
-    case DC_MAX_CURVE: e = launch_in<dc::FEAT_MAX_CURVE>(p, in_kind, j->out_kind, j->n_frames, s, v4); break;
+    case DC_RANGE: e = launch_in<dc::FEAT_RANGE>(p, in_kind, j->out_kind, j->n_frames, s, v4, fast); break;
+    case DC_BEARING: e = launch_in<dc::FEAT_BEARING>(p, in_kind, j->out_kind, j->n_frames, s, v4, fast); break;
+    case DC_FLEXION: e = launch_in<dc::FEAT_FLEXION>(p, in_kind, j->out_kind, j->n_frames, s, v4, fast); break;
+    case DC_CURVATURE: e = launch_in<dc::FEAT_CURVATURE>(p, in_kind, j->out_kind, j->n_frames, s, v4, fast); break;
+    case DC_MAX_CURVE: e = launch_in<dc::FEAT_MAX_CURVE>(p, in_kind, j->out_kind, j->n_frames, s, v4, fast); break;
     case DC_SCALE:
-        e = launch_px<dc::FEAT_SCALE, dc::IN_U16_RANGE, dc::OUT_U16>(p, j->n_frames, s, v4);
+        e = launch_px<dc::FEAT_SCALE, dc::IN_U16_RANGE, dc::OUT_U16>(p, j->n_frames, s, v4, false);
         break;
     default: return fail(c, DC_ERR_INVALID, "unknown feature");
     }

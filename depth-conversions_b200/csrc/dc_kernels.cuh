@@ -64,11 +64,12 @@ struct in_elem<IN_F32_RANGE> {
 template <int PX>
 __device__ __forceinline__ void load_vec(const unsigned short* p, float (&o)[PX]) {
     if constexpr (PX == 4) {
+        // 2^23 + v has v in its low mantissa bits: PRMT + FADD instead of I2F
         const uint2 r = __ldg(reinterpret_cast<const uint2*>(p));
-        o[0]          = float(r.x & 0xffffu);
-        o[1]          = float(r.x >> 16);
-        o[2]          = float(r.y & 0xffffu);
-        o[3]          = float(r.y >> 16);
+        o[0] = sub(__uint_as_float(__byte_perm(r.x, 0x4b000000u, 0x7410)), 8388608.0f);
+        o[1] = sub(__uint_as_float(__byte_perm(r.x, 0x4b000000u, 0x7432)), 8388608.0f);
+        o[2] = sub(__uint_as_float(__byte_perm(r.y, 0x4b000000u, 0x7410)), 8388608.0f);
+        o[3] = sub(__uint_as_float(__byte_perm(r.y, 0x4b000000u, 0x7432)), 8388608.0f);
     } else {
 #pragma unroll
         for (int i = 0; i < PX; ++i)
@@ -187,7 +188,7 @@ __device__ __forceinline__ void store_vec(unsigned short* p,
 }
 
 // ---------------------------------------------------------------------------
-template <int FEAT, int IN, int OUT, int PX>
+template <int FEAT, int IN, int OUT, int PX, bool FAST>
 __global__ void __launch_bounds__(256)
     feature_kernel(const __grid_constant__ kparams p) {
     using TI = typename in_elem<IN>::type;
@@ -230,11 +231,25 @@ __global__ void __launch_bounds__(256)
         float up[PX + 2], mid[PX + 2], dn[PX + 2];
         const bool want_up = p.out[1] != nullptr || p.out[2] != nullptr;
         const bool want_dn = p.out[3] != nullptr;
+#pragma unroll
+        for (int i = 0; i < PX + 2; ++i)
+            up[i] = dn[i] = 0.0f;
         if (want_up)
             load_range_row<IN, PX, true, false>(p, frame, v - 1, u0, up);
         load_range_row<IN, PX, true, false>(p, frame, v, u0, mid);
         if (want_dn)
             load_range_row<IN, PX, true, false>(p, frame, v + 1, u0, dn);
+        // squares and doubles shared by the four directions and by neighbours
+        float sq_up[PX + 1], sq_mid[PX + 1], sq_dn[PX + 1], b2[PX];
+#pragma unroll
+        for (int i = 0; i < PX + 1; ++i) {
+            sq_up[i]  = mul(up[i], up[i]);
+            sq_mid[i] = mul(mid[i], mid[i]);
+            sq_dn[i]  = mul(dn[i], dn[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < PX; ++i)
+            b2[i] = mul(2.0f, mid[i + 1]);
 #pragma unroll
         for (int d = 0; d < 4; ++d) {
             if (p.out[d] == nullptr)
@@ -244,25 +259,32 @@ __global__ void __launch_bounds__(256)
             TO o[PX];
 #pragma unroll
             for (int i = 0; i < PX; ++i) {
-                const int  u = u0 + i;
-                float      prior;
-                bool       valid;
+                const int u = u0 + i;
+                float     prior, prior_sq;
+                bool      valid;
                 if (d == 0) {
-                    prior = mid[i];
+                    prior = mid[i], prior_sq = sq_mid[i];
                     valid = u >= 1;
                 } else if (d == 1) {
-                    prior = up[i + 1];
+                    prior = up[i + 1], prior_sq = sq_up[i + 1];
                     valid = v >= 1;
                 } else if (d == 2) {
-                    prior = up[i];
+                    prior = up[i], prior_sq = sq_up[i];
                     valid = u >= 1 && v >= 1;
                 } else {
-                    prior = dn[i];
+                    prior = dn[i], prior_sq = sq_dn[i];
                     valid = u >= 1 && v < h - 1;
                 }
-                const float a = valid ? bearing_pixel(mid[i + 1], prior, cs[i]) : 0.0f;
+                // outside the computed region the table holds 0: keep the
+                // arithmetic in range with a harmless cosine, discard below
+                const float ca = valid ? cs[i] : 0.5f;
+                float       b2c;
+                float       a = bearing_angle_pre<FAST>(mid[i + 1], prior, sq_mid[i + 1],
+                                                        prior_sq, b2[i], ca, b2c);
+                // depth_to_bearing.h:204-207: either depth 0 -> 0 ((2b)*c == 0)
+                a = (valid && b2c != 0.0f) ? a : 0.0f;
                 if constexpr (OUT == OUT_U16)
-                    o[i] = quant_scale(a, p.q_bearing);
+                    o[i] = quant_scale_bounded(a, p.q_bearing);
                 else
                     o[i] = a;
             }
@@ -300,13 +322,13 @@ __global__ void __launch_bounds__(256)
                 float     f = 0.0f;
                 if (row_interior && u >= 1 && u < w - 1) {
                     const int c = i + 1;
-                    f = flexion_from_points(P[0][c], P[2][c],          // (u,v-1) (u,v+1)
+                    f = flexion_from_points<FAST>(P[0][c], P[2][c],          // (u,v-1) (u,v+1)
                                             P[1][c - 1], P[1][c + 1],  // (u-1,v) (u+1,v)
                                             P[0][c + 1], P[2][c - 1],  // (u+1,v-1) (u-1,v+1)
                                             P[0][c - 1], P[2][c + 1]); // (u-1,v-1) (u+1,v+1)
                 }
                 if constexpr (OUT == OUT_U16)
-                    o[i] = quant_scale(f, 65535.0f);
+                    o[i] = quant_scale_bounded(f, 65535.0f);
                 else
                     o[i] = f;
             }
@@ -329,7 +351,7 @@ __global__ void __launch_bounds__(256)
                                 mid[c - 1] != 0.0f && mid[c] != 0.0f && mid[c + 1] != 0.0f &&
                                 dn[c - 1] != 0.0f && dn[c] != 0.0f && dn[c + 1] != 0.0f;
                 if (ok) {
-                    const derivs dv = derivatives(mid[c - 1], mid[c + 1], up[c], dn[c],
+                    const derivs dv = derivatives<FAST>(mid[c - 1], mid[c + 1], up[c], dn[c],
                                                   mid[c], a_phi[i], a_theta[i], a_pt[i]);
                     if (p.out[0] != nullptr)
                         kg = gaussian_curvature(dv);
@@ -357,7 +379,8 @@ __global__ void __launch_bounds__(256)
             //   dia1 = D(u,v)      dia2 = D(u+1,v+1)
             //   ant1 = phi((u+1,v+1),(u,v)) = D(u+1,v+1)   (sic, :136)
             //   ant2 = phi((u,v),(u+1,v-1)) = A(u+1,v-1)
-            float cH[PX + 1], cV0[PX], cV1[PX], cD0[PX], cD1[PX + 1], cA[PX + 1];
+            float cH[PX + 1] = {}, cV0[PX] = {}, cV1[PX] = {}, cD0[PX] = {}, cD1[PX + 1] = {},
+                             cA[PX + 1] = {};
             if (row_interior) {
                 load_tab<PX>(p.cosp[1], w, v, u0, cV0);
                 load_tab<PX>(p.cosp[1], w, v + 1, u0, cV1);
@@ -380,21 +403,41 @@ __global__ void __launch_bounds__(256)
                     cA[i] = t[i];
                 cA[PX] = more ? tab_at(p.cosp[3], w, v - 1, u0 + PX) : 0.0f;
             }
+            // squares of the whole window, shared by the eight angles
+            float sq_up[PX + 2], sq_mid[PX + 2], sq_dn[PX + 2];
+#pragma unroll
+            for (int i = 0; i < PX + 2; ++i) {
+                sq_up[i]  = mul(up[i], up[i]);
+                sq_mid[i] = mul(mid[i], mid[i]);
+                sq_dn[i]  = mul(dn[i], dn[i]);
+            }
             TO o[PX];
 #pragma unroll
             for (int i = 0; i < PX; ++i) {
-                const int u = u0 + i, c = i + 1;
-                float     a = 0.0f;
-                if (row_interior && u >= 1 && u < w - 1) {
-                    const float d0    = mid[c];
-                    const float a_hor = angle_formula(mid[c - 1], d0, mid[c + 1], cH[i], cH[i + 1]);
-                    const float a_ver = angle_formula(up[c], d0, dn[c], cV0[i], cV1[i]);
-                    const float a_dia = angle_formula(up[c - 1], d0, dn[c + 1], cD0[i], cD1[i + 1]);
-                    const float a_ant = angle_formula(dn[c - 1], d0, up[c + 1], cD1[i + 1], cA[i + 1]);
-                    a = fmaxf(a_hor, fmaxf(a_ver, fmaxf(a_dia, a_ant)));
-                }
+                const int  u = u0 + i, c = i + 1;
+                const bool inside = row_interior && u >= 1 && u < w - 1;
+                const float d0 = mid[c], bb = sq_mid[c], b2 = mul(2.0f, d0);
+                // angle_formula (depth_to_max_curve.h:55-82): 0 if any of the
+                // three depths is 0, else the sum of the two bearing angles
+                auto pair = [&](float dm, float sm, float dp, float sp, float c1, float c2) {
+                    c1 = inside ? c1 : 0.5f;
+                    c2 = inside ? c2 : 0.5f;
+                    float       x1, x2;
+                    const float a1 = bearing_angle_pre<FAST>(d0, dm, bb, sm, b2, c1, x1);
+                    const float a2 = bearing_angle_pre<FAST>(d0, dp, bb, sp, b2, c2, x2);
+                    return (x1 != 0.0f && x2 != 0.0f) ? add(a1, a2) : 0.0f;
+                };
+                const float a_hor = pair(mid[c - 1], sq_mid[c - 1], mid[c + 1], sq_mid[c + 1],
+                                         cH[i], cH[i + 1]);
+                const float a_ver = pair(up[c], sq_up[c], dn[c], sq_dn[c], cV0[i], cV1[i]);
+                const float a_dia = pair(up[c - 1], sq_up[c - 1], dn[c + 1], sq_dn[c + 1],
+                                         cD0[i], cD1[i + 1]);
+                const float a_ant = pair(dn[c - 1], sq_dn[c - 1], up[c + 1], sq_up[c + 1],
+                                         cD1[i + 1], cA[i + 1]);
+                float a = fmaxf(a_hor, fmaxf(a_ver, fmaxf(a_dia, a_ant)));
+                a       = inside ? a : 0.0f;
                 if constexpr (OUT == OUT_U16)
-                    o[i] = quant_scale(a, p.q_max_curve);
+                    o[i] = quant_scale_bounded(a, p.q_max_curve);
                 else
                     o[i] = a;
             }

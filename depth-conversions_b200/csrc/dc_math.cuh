@@ -9,6 +9,8 @@
 #ifndef DC_MATH_CUH
 #define DC_MATH_CUH
 
+#include "dc_fastmath.cuh"
+
 #include <cuda_runtime.h>
 
 namespace dc {
@@ -43,13 +45,30 @@ __device__ __forceinline__ vec3 sub3(const vec3& a, const vec3& b) {
     return {sub(a.x, b.x), sub(a.y, b.y), sub(a.z, b.z)};
 }
 // Eigen 3.3.7 Core/Dot.h:124-134: z = squaredNorm; z > 0 ? n / sqrt(z) : n
+//
+// FAST: the three divisions share one refined reciprocal, seeded from the
+// rsqrt of the square-root step (tests/cuda/mathcheck.cu "normalise_shared_rcp":
+// bit-identical to __fdiv_rn(x, __fsqrt_rn(z))). z == 0 happens only for the
+// null vector, which must be returned unchanged: clamping z to 2^-100 makes the
+// divisions yield 0 = the input without a branch. Needs z == 0 or z >= 2^-100
+// and quotients that are 0 or normal: guaranteed per camera (dc_tables.cpp
+// fast_ok) for u16 depths.
+template <bool FAST>
 __device__ __forceinline__ vec3 normalized3(const vec3& n) {
     const float z = dot3(n, n);
-    if (z > 0.0f) {
-        const float s = sqrt_rn(z);
-        return {div(n.x, s), div(n.y, s), div(n.z, s)};
+    if constexpr (FAST) {
+        float       h;
+        const float s = sqrt_rn_fast(fmaxf(z, 7.888609052210118e-31f), h);
+        const float y = rcp_refined(s, add(h, h));
+        return {div_rn_with_rcp(n.x, s, y), div_rn_with_rcp(n.y, s, y),
+                div_rn_with_rcp(n.z, s, y)};
+    } else {
+        if (z > 0.0f) {
+            const float s = sqrt_rn(z);
+            return {div(n.x, s), div(n.y, s), div(n.z, s)};
+        }
+        return n;
     }
-    return n;
 }
 // Eigen 3.3.7 Geometry/OrthoMethods.h:34-46
 __device__ __forceinline__ vec3 cross3(const vec3& a, const vec3& b) {
@@ -57,41 +76,51 @@ __device__ __forceinline__ vec3 cross3(const vec3& a, const vec3& b) {
             sub(mul(a.x, b.y), mul(a.y, b.x))};
 }
 
-// math/triangles.h:27-64 bearing_angle(b, c, cos_alpha)
-__device__ __forceinline__ float bearing_angle(float b, float c, float cos_alpha) {
+// math/triangles.h:27-64 bearing_angle(b, c, cos_alpha), with bb = b*b,
+// cc = c*c and b2 = 2*b passed in (shared between directions / neighbours).
+// Returns the clamped ratio's angle; `b2c` (= (2b)*c) is handed back so callers
+// can test "either depth is zero" on it.
+//
+// FAST (b, c in [2^-10, 2^20], cos_alpha in (0, 1 - 8e-7]): the radicand is
+// then strictly positive (b^2 + c^2 >= 2bc and the rounding errors, < 4e-7
+// relative, are smaller than 1 - cos_alpha), so the reference's "d == 0 ?
+// d + delta" never fires, and every operand of sqrt / div is normal.
+template <bool FAST>
+__device__ __forceinline__ float bearing_angle_pre(float b, float c, float bb, float cc,
+                                                   float b2, float cos_alpha, float& b2c) {
     const float nom = sub(b, mul(c, cos_alpha));
-    const float sum = add(mul(b, b), mul(c, c));
-    const float m   = mul(mul(mul(2.0f, b), c), cos_alpha);
-    const float d   = sqrt_rn(sub(sum, m));
-    const float den = (d == 0.0f) ? add(d, DC_DELTA) : d;
-    const float r   = clamp(div(nom, den), DC_MINUS_ONE_PLUS_DELTA, DC_ONE_MINUS_DELTA);
-    return acosf(r);
+    const float sum = add(bb, cc);
+    b2c             = mul(b2, c);
+    const float rad = sub(sum, mul(b2c, cos_alpha));
+    float       q;
+    if constexpr (FAST) {
+        float       h;
+        const float d = sqrt_rn_fast(fmaxf(rad, 7.888609052210118e-31f), h);
+        q             = div_rn_with_rcp(nom, d, rcp_refined(d, add(h, h)));
+    } else {
+        const float d   = sqrt_rn(rad);
+        const float den = (d == 0.0f) ? add(d, DC_DELTA) : d;
+        q               = div(nom, den);
+    }
+    return acos_rel(clamp(q, DC_MINUS_ONE_PLUS_DELTA, DC_ONE_MINUS_DELTA));
 }
-
-// conversion/depth_to_bearing.h:204-208: 0 when either depth is 0
-__device__ __forceinline__ float bearing_pixel(float d_i, float d_j, float cos_alpha) {
-    return (d_i == 0.0f || d_j == 0.0f) ? 0.0f : bearing_angle(d_i, d_j, cos_alpha);
-}
-
-// conversion/depth_to_max_curve.h:55-82 angle_formula
-__device__ __forceinline__ float angle_formula(float d__1, float d__0, float d_1,
-                                               float cos_alpha1, float cos_alpha2) {
-    if (d__1 == 0.0f || d__0 == 0.0f || d_1 == 0.0f)
-        return 0.0f;
-    return add(bearing_angle(d__0, d__1, cos_alpha1),
-               bearing_angle(d__0, d_1, cos_alpha2));
+template <bool FAST>
+__device__ __forceinline__ float bearing_angle(float b, float c, float cos_alpha) {
+    float b2c;
+    return bearing_angle_pre<FAST>(b, c, mul(b, b), mul(c, c), mul(2.0f, b), cos_alpha, b2c);
 }
 
 // conversion/depth_to_flexion.h:105-135, given the eight neighbour points
 // P = d * ray already multiplied out (to_camera, :70-76).
+template <bool FAST>
 __device__ __forceinline__ float flexion_from_points(const vec3& p0, const vec3& p1,
                                                      const vec3& p2, const vec3& p3,
                                                      const vec3& p4, const vec3& p5,
                                                      const vec3& p6, const vec3& p7) {
-    const vec3  n0 = normalized3(sub3(p1, p0));
-    const vec3  n1 = normalized3(sub3(p3, p2));
-    const vec3  n2 = normalized3(sub3(p5, p4));
-    const vec3  n3 = normalized3(sub3(p7, p6));
+    const vec3  n0 = normalized3<FAST>(sub3(p1, p0));
+    const vec3  n1 = normalized3<FAST>(sub3(p3, p2));
+    const vec3  n2 = normalized3<FAST>(sub3(p5, p4));
+    const vec3  n3 = normalized3<FAST>(sub3(p7, p6));
     const vec3  c0 = cross3(n0, n1);
     const vec3  c1 = cross3(n2, n3);
     return clamp(fabsf(dot3(c0, c1)), 0.0f, 1.0f);
@@ -102,6 +131,17 @@ struct derivs {
 };
 // math/derivatives.h:17-40, 66-93. left/right = (u-1,v)/(u+1,v), up/down =
 // (u,v-1)/(u,v+1). f_uv uses the VERTICAL neighbours with d_phi_theta (sic).
+// FAST: ray angles lie in [1.5e-3, pi] (checked per camera) and depths in
+// [2^-10, 2^20], so each numerator is 0 or >= 2^-34 in magnitude and every
+// quotient is 0 or normal: the guard-free division is exact.
+template <bool FAST>
+__device__ __forceinline__ float div_sel(float a, float b) {
+    if constexpr (FAST)
+        return div_rn_fast(a, b);
+    else
+        return div(a, b);
+}
+template <bool FAST>
 __device__ __forceinline__ derivs derivatives(float left, float right, float up,
                                               float down, float centre, float d_phi,
                                               float d_theta, float d_phi_theta) {
@@ -109,11 +149,17 @@ __device__ __forceinline__ derivs derivatives(float left, float right, float up,
     const float two_c = mul(2.0f, centre);
     const float sh    = sub(add(right, left), two_c);
     const float sv    = sub(add(down, up), two_c);
-    r.f_u             = div(sub(right, left), mul(2.0f, d_phi));
-    r.f_v             = div(sub(down, up), mul(2.0f, d_theta));
-    r.f_uu            = div(sh, mul(d_phi, d_phi));
-    r.f_vv            = div(sv, mul(d_theta, d_theta));
-    r.f_uv            = div(sv, mul(d_phi_theta, d_phi_theta));
+    r.f_u             = div_sel<FAST>(sub(right, left), mul(2.0f, d_phi));
+    r.f_v             = div_sel<FAST>(sub(down, up), mul(2.0f, d_theta));
+    r.f_uu            = div_sel<FAST>(sh, mul(d_phi, d_phi));
+    if constexpr (FAST) {
+        // f_vv and f_uv divide the same numerator
+        r.f_vv = div_rn_fast(sv, mul(d_theta, d_theta));
+        r.f_uv = div_rn_fast(sv, mul(d_phi_theta, d_phi_theta));
+    } else {
+        r.f_vv = div(sv, mul(d_theta, d_theta));
+        r.f_uv = div(sv, mul(d_phi_theta, d_phi_theta));
+    }
     return r;
 }
 // math/curvature.h:18-23
@@ -151,6 +197,14 @@ __device__ __forceinline__ unsigned short sat_u16_rn(float v) {
 // convertTo(CV_16U, alpha, 0) on a float source
 __device__ __forceinline__ unsigned short quant_scale(float v, float alpha) {
     return sat_u16_rn(mul(v, alpha));
+}
+// The same for features with a known bound (bearing in [0, pi), flexion in
+// [0, 1], max-curve in [0, 2 pi)): 0 <= v*alpha < 2^22, so round-half-to-even
+// is one FADD with 1.5 * 2^23 and the integer sits in the low mantissa bits --
+// no F2I on the XU pipe. min() only guards the upper clamp of convertTo.
+__device__ __forceinline__ unsigned short quant_scale_bounded(float v, float alpha) {
+    const float x = fminf(mul(v, alpha), 65535.0f);
+    return (unsigned short)(__float_as_uint(add(x, 12582912.0f)) & 0xffffu);
 }
 // math/scaling.h:29-55 scale({lo,hi},{0,65535}, v) then gsl::narrow_cast<ushort>
 // (truncation), conversion/depth_to_curvature.h:239-243; masked by

@@ -142,6 +142,29 @@ void build_rays(tables& t) {
     }
 }
 
+// range proof for the guard-free arithmetic: all valid entries in [lo, hi]
+bool all_within(const std::vector<float>& v, int w, int u0, int u1, int v0, int v1, float lo,
+                float hi) {
+    for (int y = v0; y < v1; ++y)
+        for (int x = u0; x < u1; ++x) {
+            const float f = v[std::size_t(y) * w + x];
+            if (!(f >= lo && f <= hi))
+                return false;
+        }
+    return true;
+}
+
+bool rays_in_fast_range(const tables& t) {
+    const float tiny = 9.094947017729282e-13f;  // 2^-40
+    for (const std::vector<float>* r : {&t.ray_x, &t.ray_y, &t.ray_z})
+        for (float f : *r) {
+            const float a = std::fabs(f);
+            if (!(a == 0.0f || (a >= tiny && a <= 1.0f)))
+                return false;
+        }
+    return true;
+}
+
 void finish_uniform(table& tb, int w, int h, int u0, int u1, int v0, int v1) {
     // uniform iff every entry of the valid region [u0,u1) x [v0,v1) is equal
     tb.uniform = false;
@@ -181,6 +204,7 @@ void build_range_factor(tables& t) {
         });
     }
     finish_uniform(t.range_factor, c.w, c.h, 0, c.w, 0, c.h);
+    t.fast_ok = t.fast_ok && all_within(t.range_factor.v, c.w, 0, c.w, 0, c.h, 1.0f, 64.0f);
 }
 
 void build_cos_prior(tables& t) {
@@ -203,6 +227,8 @@ void build_cos_prior(tables& t) {
                 }
         });
         finish_uniform(tb, w, h, xs[d], w, ys[d], h - ye[d]);
+        t.fast_ok = t.fast_ok &&
+                    all_within(tb.v, w, xs[d], w, ys[d], h - ye[d], 0.5f, 1.0f - 8e-7f);
     }
 }
 
@@ -231,6 +257,8 @@ void build_curv_angles(tables& t) {
     finish_uniform(t.d_phi, w, h, 1, w - 1, 1, h - 1);
     finish_uniform(t.d_theta, w, h, 1, w - 1, 1, h - 1);
     finish_uniform(t.d_phi_theta, w, h, 1, w - 1, 1, h - 1);
+    for (const table* tb : {&t.d_phi, &t.d_theta, &t.d_phi_theta})
+        t.fast_ok = t.fast_ok && all_within(tb->v, w, 1, w - 1, 1, h - 1, 1e-3f, 3.2f);
 }
 
 }  // namespace
@@ -239,8 +267,10 @@ void build_tables(tables& t, unsigned need) {
     if (t.cam.model == camera_model::none)
         return;
     const bool want_rays = (need & (NEED_RAYS | NEED_COS_PRIOR | NEED_CURV_ANGLES)) != 0;
-    if (want_rays && t.ray_x.empty())
+    if (want_rays && t.ray_x.empty()) {
         build_rays(t);
+        t.fast_ok = t.fast_ok && rays_in_fast_range(t);
+    }
     if ((need & NEED_RANGE_FACTOR) && t.range_factor.v.empty())
         build_range_factor(t);
     if ((need & NEED_COS_PRIOR) && t.cos_prior[0].v.empty())

@@ -43,6 +43,12 @@ struct tables {
     // phi over the 2-pixel spans curvature uses: d_phi (u-1,v)-(u+1,v),
     // d_theta (u,v-1)-(u,v+1), d_phi_theta (u-1,v-1)-(u+1,v+1); 1 at the border.
     table d_phi, d_theta, d_phi_theta;
+    // True while every table built so far stays inside the value ranges for
+    // which the kernels' guard-free exact division / square root are proven
+    // (dc_fastmath.cuh): range factor in [1, 64], cos_prior in [0.5, 1 - 8e-7],
+    // non-zero ray components >= 2^-40 in magnitude, curvature angles in
+    // [1e-3, 3.2]. Otherwise the kernels with the IEEE intrinsics are used.
+    bool fast_ok = true;
 };
 
 enum table_need : unsigned {

@@ -1,0 +1,144 @@
+// GPU self-check of depth-conversions_b200/csrc/dc_fastmath.cuh against the
+// IEEE intrinsics (__fsqrt_rn, __fdiv_rn) and double-precision acos.
+// Prints one line per check: "<name> checked=<n> mismatches=<m> [max_rel=<e>]".
+// Exit code 0 iff every exactness check has 0 mismatches and acos max_rel < 1e-6.
+#include "../../depth-conversions_b200/csrc/dc_fastmath.cuh"
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+
+__device__ unsigned long long splitmix(unsigned long long x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+// positive float with exponent uniform in [elo, ehi] (unbiased) and random mantissa
+__device__ float rnd_float(unsigned long long h, int elo, int ehi) {
+    const unsigned mant = unsigned(h) & 0x7fffffu;
+    const int      e    = elo + int((h >> 32) % unsigned(ehi - elo + 1));
+    return __uint_as_float((unsigned(e + 127) << 23) | mant);
+}
+
+__global__ void check_sqrt(unsigned long long* bad, unsigned lo, unsigned hi) {
+    // exhaustive over bit patterns [lo, hi]
+    const unsigned long long n = (unsigned long long)hi - lo + 1;
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const float x = __uint_as_float(lo + unsigned(i));
+        if (__float_as_uint(dc::sqrt_rn_fast(x)) != __float_as_uint(__fsqrt_rn(x)))
+            atomicAdd(bad, 1ull);
+    }
+}
+
+__global__ void check_div(unsigned long long* bad, unsigned long long n, int mode) {
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const unsigned long long h1 = splitmix(i * 2 + 0x1234567ull * mode);
+        const unsigned long long h2 = splitmix(h1 ^ 0xABCDEF12345ull);
+        float a, b;
+        if (mode == 0) {  // wide exponents
+            a = rnd_float(h1, -60, 60);
+            b = rnd_float(h2, -40, 40);
+        } else if (mode == 1) {  // bearing: |nom| vs den, ratio near +-1
+            b = rnd_float(h2, -12, 21);
+            a = b * (1.0f + float(int(h1 & 0xffff) - 32768) * 1e-7f);
+        } else {  // b with extreme mantissas (all ones / all zeros / one bit)
+            a = rnd_float(h1, -30, 30);
+            const unsigned pats[4] = {0x7fffffu, 0x000000u, 0x000001u, 0x7ffffeu};
+            b = __uint_as_float((__float_as_uint(rnd_float(h2, -30, 30)) & 0xff800000u) |
+                                pats[(h2 >> 60) & 3]);
+        }
+        if (h1 >> 63)
+            a = -a;
+        if (__float_as_uint(dc::div_rn_fast(a, b)) != __float_as_uint(__fdiv_rn(a, b)))
+            atomicAdd(bad, 1ull);
+    }
+}
+
+// normalisation as flexion does it: component / sqrt(z), reciprocal shared and
+// seeded from the rsqrt of the square root step.
+__global__ void check_norm(unsigned long long* bad, unsigned long long n) {
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const unsigned long long h1 = splitmix(i * 3 + 77);
+        const unsigned long long h2 = splitmix(h1 ^ 0x5555aaaa5555ull);
+        const float z = rnd_float(h1, -60, 60);
+        // |component| <= sqrt(z); pick a fraction of it, sometimes tiny, sometimes 0
+        const float s_ref = __fsqrt_rn(z);
+        float       a     = s_ref * __uint_as_float(0x3f800000u - unsigned(h2 & 0x3ffffffu));
+        if (((h2 >> 40) & 15) == 0)
+            a *= 1e-9f;
+        if (((h2 >> 44) & 63) == 0)
+            a = 0.0f;
+        if (h2 >> 63)
+            a = -a;
+        float       hh;
+        const float s = dc::sqrt_rn_fast(z, hh);
+        const float y = dc::rcp_refined(s, __fadd_rn(hh, hh));
+        const float q = dc::div_rn_with_rcp(a, s, y);
+        const float want = __fdiv_rn(a, s_ref);
+        if (__float_as_uint(s) != __float_as_uint(s_ref) ||
+            (__float_as_uint(q) != __float_as_uint(want) && !(q == 0.0f && want == 0.0f)))
+            atomicAdd(bad, 1ull);
+    }
+}
+
+__global__ void check_acos(unsigned long long* worst_bits) {
+    // exhaustive over |x| <= 1 - 10 eps, both signs: bit patterns [0, 0x3f7fffec]
+    const unsigned hi = __float_as_uint(1.0f - 10.0f * 1.1920928955078125e-07f);
+    double         w  = 0.0;
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+         i <= 2ull * hi + 1; i += (unsigned long long)gridDim.x * blockDim.x) {
+        const unsigned b = unsigned(i >> 1);
+        float          x = __uint_as_float(b);
+        if (i & 1)
+            x = -x;
+        const double ref = acos(double(x));
+        const double got = double(dc::acos_rel(x));
+        const double rel = fabs(got - ref) / ref;
+        w                = fmax(w, rel);
+    }
+    atomicMax(worst_bits, (unsigned long long)__double_as_longlong(w));
+}
+
+int main() {
+    unsigned long long* d;
+    cudaMalloc(&d, 8);
+    auto run = [&](const char* name, unsigned long long n, auto launch) {
+        cudaMemset(d, 0, 8);
+        launch();
+        unsigned long long h = 0;
+        const cudaError_t  e = cudaDeviceSynchronize();
+        cudaMemcpy(&h, d, 8, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) {
+            printf("%s CUDA error %s\n", name, cudaGetErrorString(e));
+            exit(2);
+        }
+        printf("%s checked=%llu mismatches=%llu\n", name, n, h);
+        return h;
+    };
+    unsigned long long bad = 0;
+    const unsigned lo = 0x0d800000u /* 2^-100 */, hi = 0x7f7fffffu;
+    bad += run("sqrt_rn_fast_exhaustive", (unsigned long long)hi - lo + 1,
+               [&] { check_sqrt<<<148 * 16, 256>>>(d, lo, hi); });
+    const unsigned long long N = 1ull << 33;
+    for (int m = 0; m < 3; ++m) {
+        char nm[64];
+        snprintf(nm, sizeof nm, "div_rn_fast_mode%d", m);
+        bad += run(nm, N, [&] { check_div<<<148 * 16, 256>>>(d, N, m); });
+    }
+    bad += run("normalise_shared_rcp", N, [&] { check_norm<<<148 * 16, 256>>>(d, N); });
+    cudaMemset(d, 0, 8);
+    check_acos<<<148 * 16, 256>>>(d);
+    cudaDeviceSynchronize();
+    unsigned long long wb = 0;
+    cudaMemcpy(&wb, d, 8, cudaMemcpyDeviceToHost);
+    double worst;
+    memcpy(&worst, &wb, 8);
+    printf("acos_rel exhaustive max_rel=%.3e\n", worst);
+    const bool ok = bad == 0 && worst < 1e-6;
+    printf("%s\n", ok ? "MATHCHECK OK" : "MATHCHECK FAILED");
+    return ok ? 0 : 1;
+}
