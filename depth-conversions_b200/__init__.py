@@ -14,7 +14,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libdepthconv_b200.so")
+LIB_PATH = os.environ.get("DC_LIB") or os.path.join(HERE, "lib", "libdepthconv_b200.so")
 HOST_LIB_PATH = os.path.join(HERE, "lib", "libdc_host.so")
 DEPTH2X_PATH = os.path.join(HERE, "bin", "depth2x")
 

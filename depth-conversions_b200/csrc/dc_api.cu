@@ -2,11 +2,13 @@
 // dispatch and the host-buffer pipeline. See include/depthconv_b200.h.
 #include "../../include/depthconv_b200.h"
 #include "dc_kernels.cuh"
+#include "dc_pair_kernels.cuh"
 #include "dc_tables.h"
 
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -236,8 +238,43 @@ int validate_job(dc_ctx* c, const dc_job* j) {
 }
 
 // ---------------------------------------------------------------------------
+// Rows a thread of the frame-pair kernels marches over (tuning knob:
+// DC_ROWS_PER_STRIP in the environment, read once).
+int rows_per_strip() {
+    static const int v = [] {
+        const char* e = std::getenv("DC_ROWS_PER_STRIP");
+        const int   n = e != nullptr ? std::atoi(e) : 0;
+        return n >= 3 ? n : 18;
+    }();
+    return v;
+}
+
+template <int FEAT>
+constexpr bool has_pair_kernel() {
+    return FEAT == dc::FEAT_BEARING || FEAT == dc::FEAT_MAX_CURVE || FEAT == dc::FEAT_CURVATURE;
+}
+
+// The frame-pair row-marching kernels (dc_pair_kernels.cuh): u16 input,
+// width % 4 == 0, aligned frames, per-camera range proof.
+template <int FEAT, int IN, int OUT>
+cudaError_t launch_pair(const dc::kparams& p, int n_frames, cudaStream_t s) {
+    const int       rps    = rows_per_strip();
+    const long long strips = (p.h + rps - 1) / rps;
+    const long long pairs  = (n_frames + 1) / 2;
+    const long long threads = pairs * strips * (p.w / 4);
+    const long long blocks  = (threads + dc::pr::kPairThreads - 1) / dc::pr::kPairThreads;
+    if (blocks > 0x7fffffffLL)
+        return cudaErrorInvalidConfiguration;
+    dc::pr::pair_kernel<FEAT, IN, OUT><<<unsigned(blocks), dc::pr::kPairThreads, 0, s>>>(p, n_frames, rps);
+    return cudaGetLastError();
+}
+
 template <int FEAT, int IN, int OUT>
 cudaError_t launch_px(const dc::kparams& p, int n_frames, cudaStream_t s, bool vec4, bool fast) {
+    if constexpr (IN != dc::IN_F32_RANGE && has_pair_kernel<FEAT>()) {
+        if (vec4 && fast)
+            return launch_pair<FEAT, IN, OUT>(p, n_frames, s);
+    }
     const int px = vec4 ? 4 : 1;
     const int qw = (p.w + px - 1) / px;
     // pick the block shape that wastes the fewest threads

@@ -1,0 +1,227 @@
+// Frame-pair, row-marching kernels for sm_100a: the fast path for u16 input.
+//
+// The exact (reference-order, IEEE-rounded) arithmetic makes every stencil
+// kernel FP32-pipe bound on B200, not HBM bound. These
+// kernels therefore minimise FP32-pipe cycles and issue slots per pixel:
+//
+//   * A thread converts the SAME pixels of TWO frames at once and keeps the two
+//     values of a pixel in one 64-bit register pair, so that all arithmetic
+//     runs as packed FFMA2 / FMUL2 / FADD2 (fma.rn.f32x2: one issue slot for
+//     two IEEE-rounded results). Per-camera table values are identical for the
+//     two frames and enter as broadcast scalar operands; vector loads and
+//     stores stay per frame and fully coalesced.
+//   * A thread owns 4 columns and marches down a strip of rows with the 3-row
+//     window (range, squares) in registers: each input row is loaded, unpacked
+//     and converted to range once instead of three times, and the column halo
+//     is two extra scalar loads per row (L1 hits) instead of a shuffle.
+//   * Compares, selects, clamps, exponent tricks and u16 packing are scalar
+//     ALU-pipe instructions, which issue beside the FMA pipe.
+//
+// Results are bit-identical to the one-frame kernels of dc_kernels.cuh (same
+// operation order; the packed instructions round each half like the scalar
+// ones). Preconditions, checked by the host: u16 input, width % 4 == 0,
+// 8-byte aligned frames, and the per-camera range proof `fast_ok`.
+#ifndef DC_PAIR_CUH
+#define DC_PAIR_CUH
+
+#include "dc_kernels.cuh"
+
+namespace dc {
+namespace pr {
+
+typedef float2 f2;
+
+__device__ __forceinline__ f2 B(float s) { return make_float2(s, s); }
+__device__ __forceinline__ f2 neg2(f2 a) { return make_float2(-a.x, -a.y); }
+// ptxas 12.9 contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even under
+// --fmad=false (the scalar .rn forms are never contracted), which breaks the
+// reference's rounding order. A product is therefore written as
+// fma(a, b, -0.0) with the -0.0 read from constant memory (opaque to ptxas):
+// RN(a*b + -0) == RN(a*b) for every a, b including signed zeros, the cost is
+// the same FMA-pipe slot, and an FFMA2 result cannot be fused into an add.
+__constant__ float k_neg_zero = -0.0f;
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) { return __ffma2_rn(a, b, make_float2(k_neg_zero, k_neg_zero)); }
+__device__ __forceinline__ f2 add2(f2 a, f2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ f2 sub2(f2 a, f2 b) { return __fadd2_rn(a, neg2(b)); }
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ f2 rsq2(f2 x) { return make_float2(mufu_rsq(x.x), mufu_rsq(x.y)); }
+__device__ __forceinline__ f2 rcp2(f2 x) { return make_float2(mufu_rcp(x.x), mufu_rcp(x.y)); }
+// x * 0.5 for normal x: exponent decrement on the ALU pipe
+__device__ __forceinline__ float halve(float x) {
+    return __uint_as_float(__float_as_uint(x) - 0x00800000u);
+}
+__device__ __forceinline__ f2 halve2(f2 x) { return make_float2(halve(x.x), halve(x.y)); }
+
+// RN(sqrt(x)) per half (dc_fastmath.cuh sqrt_rn_fast), y = the rsqrt seed.
+__device__ __forceinline__ f2 sqrt2(f2 x, f2& y) {
+    y          = rsq2(x);
+    f2       g = mul2(x, y);
+    const f2 h = halve2(y);
+    const f2 r = fma2(neg2(g), g, x);
+    return fma2(r, h, g);
+}
+// one Newton step on a reciprocal seed (dc_fastmath.cuh rcp_refined)
+__device__ __forceinline__ f2 rcp_refine2(f2 b, f2 seed) {
+    return fma2(seed, fma2(neg2(b), seed, B(1.0f)), seed);
+}
+// RN(a / b) given the refined reciprocal y of b (dc_fastmath.cuh div_rn_with_rcp)
+__device__ __forceinline__ f2 div2(f2 a, f2 b, f2 y) {
+    const f2 q = mul2(a, y);
+    const f2 r = fma2(neg2(b), q, a);
+    return fma2(y, r, q);
+}
+__device__ __forceinline__ f2 div2_fast(f2 a, f2 b) { return div2(a, b, rcp_refine2(b, rcp2(b))); }
+
+// acos(clamp(q, -1 + delta, 1 - delta)), relative error < 1.2e-6:
+// sqrt(1 - a) * P5(a), a = min(|q|, 1 - delta), reflected for q < 0.
+// A NaN q (only on lanes that are masked out afterwards) comes out finite.
+__device__ __forceinline__ f2 acos2(f2 q) {
+    const f2 a = make_float2(fminf(fabsf(q.x), DC_ONE_MINUS_DELTA),
+                             fminf(fabsf(q.y), DC_ONE_MINUS_DELTA));
+    const f2 t = sub2(B(1.0f), a);
+    const f2 s = mul2(t, rsq2(t));
+    f2       p = fma2(B(-0.004307856317609549f), a, B(0.0192753653973341f));
+    p          = fma2(p, a, B(-0.044893890619277954f));
+    p          = fma2(p, a, B(0.08785323798656464f));
+    p          = fma2(p, a, B(-0.2145095020532608f));
+    p          = fma2(p, a, B(1.5707951784133911f));
+    const f2 r = mul2(s, p);
+    const f2 m = sub2(B(3.14159274101257324f), r);
+    return make_float2(q.x < 0.0f ? m.x : r.x, q.y < 0.0f ? m.y : r.y);
+}
+
+// math/triangles.h:27-64 for both frames: b, c the two ranges, bb / cc their
+// squares, b2 = 2b, cosine of the (camera-only) ray angle broadcast.
+// b2c = (2b)*c is handed back for the "either depth is zero" test.
+__device__ __forceinline__ f2 bearing2(f2 b, f2 c, f2 bb, f2 cc, f2 b2, float cos_alpha,
+                                       f2& b2c) {
+    const f2 ca  = B(cos_alpha);
+    const f2 nom = sub2(b, mul2(c, ca));
+    const f2 sum = add2(bb, cc);
+    b2c          = mul2(b2, c);
+    const f2 rad = sub2(sum, mul2(b2c, ca));
+    f2       y;
+    const f2 d = sqrt2(rad, y);
+    const f2 q = div2(nom, d, rcp_refine2(d, y));
+    return acos2(q);
+}
+
+// ---------------------------------------------------------------------------
+// one input row of the two frames: columns u0-1 .. u0+4 as (A, B) pairs
+struct rawrow {
+    uint2    a, b;            // 4 u16 of frame A / B
+    unsigned la, lb, ra, rb;  // halo pixels (0 outside the image)
+    float4   f;               // range factor of the 4 columns
+    float    fl, fr;          // and of the halo columns
+};
+
+template <bool RIGHT>
+__device__ __forceinline__ rawrow load_raw(const kparams& p, const unsigned short* A,
+                                           const unsigned short* Bf, int r, int u0,
+                                           bool use_factor) {
+    rawrow x;
+    x.a = x.b = make_uint2(0u, 0u);
+    x.la = x.lb = x.ra = x.rb = 0u;
+    x.f                       = make_float4(1.f, 1.f, 1.f, 1.f);
+    x.fl = x.fr = 1.f;
+    if (r >= 0 && r < p.h) {
+        const size_t o = size_t(r) * p.w + u0;
+        x.a            = __ldg(reinterpret_cast<const uint2*>(A + o));
+        x.b            = __ldg(reinterpret_cast<const uint2*>(Bf + o));
+        const bool l = u0 > 0, rt = RIGHT && (u0 + 4 < p.w);
+        if (l) {
+            x.la = __ldg(A + o - 1);
+            x.lb = __ldg(Bf + o - 1);
+        }
+        if (rt) {
+            x.ra = __ldg(A + o + 4);
+            x.rb = __ldg(Bf + o + 4);
+        }
+        if (use_factor) {
+            if (p.range_factor.p == nullptr) {
+                x.f  = make_float4(p.range_factor.value, p.range_factor.value,
+                                   p.range_factor.value, p.range_factor.value);
+                x.fl = x.fr = p.range_factor.value;
+            } else {
+                x.f = __ldg(reinterpret_cast<const float4*>(p.range_factor.p + o));
+                if (l)
+                    x.fl = __ldg(p.range_factor.p + o - 1);
+                if (rt)
+                    x.fr = __ldg(p.range_factor.p + o + 4);
+            }
+        }
+    }
+    return x;
+}
+
+// 2^23 + v as a float has v in its low mantissa bits
+__device__ __forceinline__ float magic_lo(unsigned w) {
+    return __uint_as_float(__byte_perm(w, 0x4b000000u, 0x7410));
+}
+__device__ __forceinline__ float magic_hi(unsigned w) {
+    return __uint_as_float(__byte_perm(w, 0x4b000000u, 0x7432));
+}
+
+// raw -> range pairs rng[0..5] = columns u0-1 .. u0+4 (conversion/util.h:41-51:
+// float(d) * sqrtf(z); d == 0 gives 0). rng[5] only when RIGHT.
+template <int IN, bool RIGHT>
+__device__ __forceinline__ void to_range(const rawrow& x, f2 (&rng)[6]) {
+    const f2 m = B(-8388608.0f);
+    f2       d[6];
+    d[0] = make_float2(magic_lo(x.la), magic_lo(x.lb));
+    d[1] = make_float2(magic_lo(x.a.x), magic_lo(x.b.x));
+    d[2] = make_float2(magic_hi(x.a.x), magic_hi(x.b.x));
+    d[3] = make_float2(magic_lo(x.a.y), magic_lo(x.b.y));
+    d[4] = make_float2(magic_hi(x.a.y), magic_hi(x.b.y));
+    d[5] = make_float2(magic_lo(x.ra), magic_lo(x.rb));
+    const float fac[6] = {x.fl, x.f.x, x.f.y, x.f.z, x.f.w, x.fr};
+#pragma unroll
+    for (int i = 0; i < (RIGHT ? 6 : 5); ++i) {
+        rng[i] = add2(d[i], m);
+        if constexpr (IN == IN_U16_DEPTH)
+            rng[i] = mul2(rng[i], B(fac[i]));
+    }
+    if constexpr (!RIGHT)
+        rng[5] = B(0.0f);
+}
+
+__device__ __forceinline__ unsigned short q16(float magic_sum) {
+    return (unsigned short)(__float_as_uint(magic_sum) & 0xffffu);
+}
+__device__ __forceinline__ uint2 pack4(float a0, float a1, float a2, float a3) {
+    return make_uint2(__byte_perm(__float_as_uint(a0), __float_as_uint(a1), 0x5410),
+                      __byte_perm(__float_as_uint(a2), __float_as_uint(a3), 0x5410));
+}
+
+// Stores 4 pixels of frame A (.x halves) and frame B (.y halves).
+// OUT_U16: v already holds value * scale; round half to even by the magic add.
+template <int OUT>
+__device__ __forceinline__ void store4(void* base, size_t oa, size_t ob, const f2 (&v)[4]) {
+    if constexpr (OUT == OUT_U16) {
+        f2 s[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            s[i] = add2(v[i], B(12582912.0f));
+        unsigned short* o = static_cast<unsigned short*>(base);
+        *reinterpret_cast<uint2*>(o + oa) = pack4(s[0].x, s[1].x, s[2].x, s[3].x);
+        *reinterpret_cast<uint2*>(o + ob) = pack4(s[0].y, s[1].y, s[2].y, s[3].y);
+    } else {
+        float* o = static_cast<float*>(base);
+        *reinterpret_cast<float4*>(o + oa) = make_float4(v[0].x, v[1].x, v[2].x, v[3].x);
+        *reinterpret_cast<float4*>(o + ob) = make_float4(v[0].y, v[1].y, v[2].y, v[3].y);
+    }
+}
+
+// table values of the 4 columns of row v (scalar when the table is uniform)
+__device__ __forceinline__ float4 tab4(const tab_ref& t, int w, int v, int u0) {
+    if (t.p == nullptr)
+        return make_float4(t.value, t.value, t.value, t.value);
+    return __ldg(reinterpret_cast<const float4*>(t.p + size_t(v) * w + u0));
+}
+__device__ __forceinline__ float tab1(const tab_ref& t, int w, int v, int u) {
+    return t.p == nullptr ? t.value : __ldg(t.p + size_t(v) * w + u);
+}
+
+}  // namespace pr
+}  // namespace dc
+#endif

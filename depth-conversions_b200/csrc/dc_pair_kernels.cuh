@@ -1,0 +1,395 @@
+// The frame-pair row-marching kernels (see dc_pair.cuh for the design).
+#ifndef DC_PAIR_KERNELS_CUH
+#define DC_PAIR_KERNELS_CUH
+
+#include "dc_pair.cuh"
+
+namespace dc {
+namespace pr {
+
+constexpr int kPairThreads = 128;
+
+// One window row: range of columns u0-1 .. u0+4 of both frames, plus (curvature
+// only) the minimum over each 3-column neighbourhood for the "any of the nine
+// depths is zero" test.
+template <int FEAT>
+struct wrow {
+    f2 r[6];
+    f2 m3[FEAT == FEAT_CURVATURE ? 4 : 1];
+};
+
+template <int FEAT>
+struct feat_traits {
+    static constexpr bool right = FEAT != FEAT_BEARING;  // needs column u0+4
+};
+
+template <int FEAT, int IN>
+__device__ __forceinline__ void commit(const rawrow& raw, wrow<FEAT>& dst) {
+    to_range<IN, feat_traits<FEAT>::right>(raw, dst.r);
+    if constexpr (FEAT == FEAT_CURVATURE) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            dst.m3[i] = make_float2(fminf(fminf(dst.r[i].x, dst.r[i + 1].x), dst.r[i + 2].x),
+                                    fminf(fminf(dst.r[i].y, dst.r[i + 1].y), dst.r[i + 2].y));
+    }
+}
+
+struct pos {
+    int    v, u0;
+    size_t oa, ob;   // element offset of (frame, v, u0) in frame A / B
+    float  inside[4];  // 1 for pixels a 3x3 stencil computes, else 0 (border)
+};
+
+// ---- per-row camera tables, fetched one row ahead --------------------------
+template <int FEAT>
+struct rtabs {};
+template <>
+struct rtabs<FEAT_BEARING> {
+    float4 c[4];
+};
+template <>
+struct rtabs<FEAT_MAX_CURVE> {
+    float cH[5], cV0[4], cV1[4], cD0[4], cD1[5], cA[5];
+};
+template <>
+struct rtabs<FEAT_CURVATURE> {
+    float4 phi, theta, pt;
+};
+
+__device__ __forceinline__ void put4(float* d, float4 v) {
+    d[0] = v.x, d[1] = v.y, d[2] = v.z, d[3] = v.w;
+}
+
+template <int FEAT>
+__device__ __forceinline__ rtabs<FEAT> load_tabs(const kparams& p, int v, int u0) {
+    rtabs<FEAT> t;
+    const int   w = p.w, h = p.h;
+    if constexpr (FEAT == FEAT_BEARING) {
+        const bool in = v >= 0 && v < h;
+#pragma unroll
+        for (int d = 0; d < 4; ++d)
+            t.c[d] = (in && p.out[d] != nullptr) ? tab4(p.cosp[d], w, v, u0)
+                                                 : make_float4(.5f, .5f, .5f, .5f);
+    } else if constexpr (FEAT == FEAT_MAX_CURVE) {
+        // depth_to_max_curve.h:113-139: all eight phi() are angles between a
+        // pixel and one of its bearing "prior" neighbours (see dc_kernels.cuh)
+        const bool  in   = v >= 1 && v < h - 1;
+        const bool  more = u0 + 4 < w;
+        const float dflt = 0.5f;
+        float4      f    = make_float4(dflt, dflt, dflt, dflt);
+        put4(t.cH, in ? tab4(p.cosp[0], w, v, u0) : f);
+        t.cH[4] = (in && more) ? tab1(p.cosp[0], w, v, u0 + 4) : dflt;
+        put4(t.cV0, in ? tab4(p.cosp[1], w, v, u0) : f);
+        put4(t.cV1, in ? tab4(p.cosp[1], w, v + 1, u0) : f);
+        put4(t.cD0, in ? tab4(p.cosp[2], w, v, u0) : f);
+        put4(t.cD1, in ? tab4(p.cosp[2], w, v + 1, u0) : f);
+        t.cD1[4] = (in && more) ? tab1(p.cosp[2], w, v + 1, u0 + 4) : dflt;
+        put4(t.cA, in ? tab4(p.cosp[3], w, v - 1, u0) : f);
+        t.cA[4] = (in && more) ? tab1(p.cosp[3], w, v - 1, u0 + 4) : dflt;
+    } else if constexpr (FEAT == FEAT_CURVATURE) {
+        const bool   in = v >= 1 && v < h - 1;
+        const float4 f  = make_float4(1.f, 1.f, 1.f, 1.f);
+        t.phi           = in ? tab4(p.d_phi, w, v, u0) : f;
+        t.theta         = in ? tab4(p.d_theta, w, v, u0) : f;
+        t.pt            = in ? tab4(p.d_phi_theta, w, v, u0) : f;
+    }
+    return t;
+}
+
+// ---- bearing: conversion/depth_to_bearing.h:185-214 ------------------------
+template <int OUT>
+__device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BEARING>& up,
+                                            const wrow<FEAT_BEARING>& mid,
+                                            const wrow<FEAT_BEARING>& dn,
+                                            const rtabs<FEAT_BEARING>& tb, const pos& at) {
+    f2 su[5], sm[5], sd[4];
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+        su[i] = mul2(up.r[i], up.r[i]);
+        sm[i] = mul2(mid.r[i], mid.r[i]);
+        if (i < 4)
+            sd[i] = mul2(dn.r[i], dn.r[i]);
+    }
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        if (p.out[d] == nullptr)
+            continue;
+        const float cs[4] = {tb.c[d].x, tb.c[d].y, tb.c[d].z, tb.c[d].w};
+        f2          o[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const f2 b = mid.r[i + 1], bb = sm[i + 1];
+            const f2 b2 = add2(b, b);
+            // prior pixel: hor (u-1,v), ver (u,v-1), dia (u-1,v-1), anti (u-1,v+1)
+            const f2 c  = d == 0 ? mid.r[i] : d == 1 ? up.r[i + 1] : d == 2 ? up.r[i] : dn.r[i];
+            const f2 cc = d == 0 ? sm[i] : d == 1 ? su[i + 1] : d == 2 ? su[i] : sd[i];
+            f2       b2c;
+            f2       a = bearing2(b, c, bb, cc, b2, cs[i], b2c);
+            // depth_to_bearing.h:204-207: either depth 0 (or the prior pixel
+            // outside the image, which reads as 0) -> 0
+            a.x  = b2c.x != 0.0f ? a.x : 0.0f;
+            a.y  = b2c.y != 0.0f ? a.y : 0.0f;
+            o[i] = OUT == OUT_U16 ? mul2(a, B(p.q_bearing)) : a;
+        }
+        store4<OUT>(p.out[d], at.oa, at.ob, o);
+    }
+}
+
+// ---- max-curve: conversion/depth_to_max_curve.h:55-153 ---------------------
+template <int OUT>
+__device__ __forceinline__ void max_curve_row(const kparams& p, const wrow<FEAT_MAX_CURVE>& up,
+                                              const wrow<FEAT_MAX_CURVE>& mid,
+                                              const wrow<FEAT_MAX_CURVE>& dn,
+                                              const rtabs<FEAT_MAX_CURVE>& tb, const pos& at) {
+    f2 su[6], sm[6], sd[6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        su[i] = mul2(up.r[i], up.r[i]);
+        sm[i] = mul2(mid.r[i], mid.r[i]);
+        sd[i] = mul2(dn.r[i], dn.r[i]);
+    }
+    f2 o[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int c  = i + 1;
+        const f2  d0 = mid.r[c], bb = sm[c], b2 = add2(d0, d0);
+        // angle_formula (:55-82): 0 if any of the three depths is 0, else the
+        // sum of the two bearing angles
+        auto pair = [&](f2 dm, f2 smm, f2 dp, f2 spp, float c1, float c2) {
+            f2       x1, x2;
+            const f2 a1 = bearing2(d0, dm, bb, smm, b2, c1, x1);
+            const f2 a2 = bearing2(d0, dp, bb, spp, b2, c2, x2);
+            const f2 s  = add2(a1, a2);
+            return make_float2((x1.x != 0.0f && x2.x != 0.0f) ? s.x : 0.0f,
+                               (x1.y != 0.0f && x2.y != 0.0f) ? s.y : 0.0f);
+        };
+        const f2 ah = pair(mid.r[c - 1], sm[c - 1], mid.r[c + 1], sm[c + 1], tb.cH[i], tb.cH[i + 1]);
+        const f2 av = pair(up.r[c], su[c], dn.r[c], sd[c], tb.cV0[i], tb.cV1[i]);
+        const f2 ad = pair(up.r[c - 1], su[c - 1], dn.r[c + 1], sd[c + 1], tb.cD0[i], tb.cD1[i + 1]);
+        const f2 aa = pair(dn.r[c - 1], sd[c - 1], up.r[c + 1], su[c + 1], tb.cD1[i + 1], tb.cA[i + 1]);
+        f2       a  = make_float2(fmaxf(fmaxf(ah.x, av.x), fmaxf(ad.x, aa.x)),
+                                  fmaxf(fmaxf(ah.y, av.y), fmaxf(ad.y, aa.y)));
+        a           = mul2(a, B(at.inside[i]));  // border stays 0 (:101-102)
+        o[i]        = OUT == OUT_U16 ? mul2(a, B(p.q_max_curve)) : a;
+    }
+    store4<OUT>(p.out[0], at.oa, at.ob, o);
+    if (p.out[1] != nullptr) {
+        // the fused `range` output (converter_laserscan.h.inl:9-10):
+        // convertTo(CV_16U) = saturate(round half even); range >= 0
+        f2 r[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            r[i] = mid.r[i + 1];
+            if constexpr (OUT == OUT_U16)
+                r[i] = make_float2(fminf(r[i].x, 65535.0f), fminf(r[i].y, 65535.0f));
+        }
+        store4<OUT>(p.out[1], at.oa, at.ob, r);
+    }
+}
+
+// ---- curvature: depth_to_curvature.h:97-206, math/derivatives.h:66-93,
+//      math/curvature.h:18-44 ------------------------------------------------
+struct curv_consts {
+    float q_div, q_rcp;  // hi - lo and its refined reciprocal (u16 output)
+};
+
+template <int OUT>
+__device__ __forceinline__ void curvature_row(const kparams& p, const wrow<FEAT_CURVATURE>& up,
+                                              const wrow<FEAT_CURVATURE>& mid,
+                                              const wrow<FEAT_CURVATURE>& dn,
+                                              const rtabs<FEAT_CURVATURE>& tb, const pos& at,
+                                              const curv_consts& cc) {
+    const float phi[4] = {tb.phi.x, tb.phi.y, tb.phi.z, tb.phi.w};
+    const float the[4] = {tb.theta.x, tb.theta.y, tb.theta.z, tb.theta.w};
+    const float pt[4]  = {tb.pt.x, tb.pt.y, tb.pt.z, tb.pt.w};
+    f2          g[4], m[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int c = i + 1;
+        // camera-only divisors, shared by the two frames: scalar
+        const float b_u = mul(2.0f, phi[i]), b_v = mul(2.0f, the[i]);
+        const float b_uu = mul(phi[i], phi[i]), b_vv = mul(the[i], the[i]);
+        const float b_uv = mul(pt[i], pt[i]);
+        const float y_u = rcp_refined(b_u, mufu_rcp(b_u)), y_v = rcp_refined(b_v, mufu_rcp(b_v));
+        const float y_uu = rcp_refined(b_uu, mufu_rcp(b_uu));
+        const float y_vv = rcp_refined(b_vv, mufu_rcp(b_vv));
+        const float y_uv = rcp_refined(b_uv, mufu_rcp(b_uv));
+        const f2    left = mid.r[c - 1], right = mid.r[c + 1], upv = up.r[c], down = dn.r[c];
+        const f2    two_c = add2(mid.r[c], mid.r[c]);
+        const f2    sh = sub2(add2(right, left), two_c);
+        const f2    sv = sub2(add2(down, upv), two_c);
+        const f2    f_u  = div2(sub2(right, left), B(b_u), B(y_u));
+        const f2    f_v  = div2(sub2(down, upv), B(b_v), B(y_v));
+        const f2    f_uu = div2(sh, B(b_uu), B(y_uu));
+        const f2    f_vv = div2(sv, B(b_vv), B(y_vv));
+        const f2    f_uv = div2(sv, B(b_uv), B(y_uv));  // sic: derivatives.h:83-90
+        const f2    fu2 = mul2(f_u, f_u), fv2 = mul2(f_v, f_v);
+        const f2    dd = add2(add2(B(1.0f), fu2), fv2);
+        // DIFF_STAR (:97-115): any of the nine depths zero -> exactly 0
+        const float mna = fminf(fminf(up.m3[i].x, mid.m3[i].x), dn.m3[i].x);
+        const float mnb = fminf(fminf(up.m3[i].y, mid.m3[i].y), dn.m3[i].y);
+        const bool  oka = mna != 0.0f, okb = mnb != 0.0f;
+        f2          kg = B(0.0f), km = B(0.0f);
+        if (p.out[0] != nullptr) {
+            const f2 n = sub2(mul2(f_uu, f_vv), mul2(f_uv, f_uv));
+            kg         = div2_fast(n, dd);
+            // n can be -0 (f_uu < 0, f_vv = f_uv = +0); the residual step
+            // would turn the quotient into +0. dd > 0: the zero keeps n's sign.
+            kg = make_float2(n.x == 0.0f ? n.x : kg.x, n.y == 0.0f ? n.y : kg.y);
+            kg         = make_float2(oka ? kg.x : 0.0f, okb ? kg.y : 0.0f);
+        }
+        if (p.out[1] != nullptr) {
+            const f2 t0  = mul2(add2(B(1.0f), fv2), f_uu);
+            const f2 t1  = mul2(mul2(add2(f_u, f_u), f_v), f_uv);
+            const f2 t2  = mul2(add2(B(1.0f), fu2), f_vv);
+            const f2 num = add2(sub2(t0, t1), t2);
+            f2       y;
+            const f2 rt = sqrt2(dd, y);
+            const f2 x  = add2(rt, rt);
+            // pow(x, 3.f): x*x*x with an exact-product correction, rounded once
+            // (glibc powf is correctly rounded in all but ~1e-4 of cases)
+            const f2 x2h = mul2(x, x);
+            const f2 x2l = fma2(x, x, neg2(x2h));
+            const f2 ph  = mul2(x2h, x);
+            const f2 pe  = fma2(x2h, x, neg2(ph));
+            const f2 den = add2(ph, fma2(x2l, x, pe));
+            km           = div2_fast(num, den);
+            km           = make_float2(oka ? km.x : 0.0f, okb ? km.y : 0.0f);
+        }
+        if constexpr (OUT == OUT_U16) {
+            // math/scaling.h:29-55 scale({lo,hi},{0,65535},v), truncated
+            // (depth_to_curvature.h:239-243), zero where the depth is invalid
+            // (:266-275). FADD.RZ with 2^23 truncates for 0 <= x < 2^23.
+            const bool ca = mid.r[c].x != 0.0f, cb = mid.r[c].y != 0.0f;
+            auto       q  = [&](f2 v) {
+                const f2 a  = mul2(B(65535.0f), sub2(v, B(p.lo)));
+                f2       s  = div2(a, B(cc.q_div), B(cc.q_rcp));
+                s           = make_float2(fminf(fmaxf(s.x, 0.0f), 65535.0f),
+                                          fminf(fmaxf(s.y, 0.0f), 65535.0f));
+                const f2 t  = __fadd2_rz(s, B(8388608.0f));
+                // store4 adds 1.5*2^23 and keeps the low 16 bits: hand it the
+                // integer as an exactly representable float
+                const f2 iv = sub2(t, B(8388608.0f));
+                return make_float2(ca ? iv.x : 0.0f, cb ? iv.y : 0.0f);
+            };
+            g[i] = q(kg);
+            m[i] = q(km);
+        } else {
+            g[i] = kg;
+            m[i] = km;
+        }
+    }
+    if (p.out[0] != nullptr)
+        store4<OUT>(p.out[0], at.oa, at.ob, g);
+    if (p.out[1] != nullptr)
+        store4<OUT>(p.out[1], at.oa, at.ob, m);
+}
+
+// ---------------------------------------------------------------------------
+template <int FEAT>
+constexpr int min_blocks() {
+#ifdef DC_MIN_BLOCKS
+    return DC_MIN_BLOCKS;
+#else
+    return FEAT == FEAT_BEARING ? 5 : 4;
+#endif
+}
+
+template <int FEAT, int IN, int OUT>
+__global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT>())
+    pair_kernel(const __grid_constant__ kparams p, int n_frames, int rows_per_strip) {
+    const int       groups_x = p.w >> 2;
+    const int       strips   = (p.h + rows_per_strip - 1) / rows_per_strip;
+    const long long gid      = (long long)blockIdx.x * kPairThreads + threadIdx.x;
+    const int       gx       = int(gid % groups_x);
+    const long long t        = gid / groups_x;
+    const int       strip    = int(t % strips);
+    const long long fp       = t / strips;
+    if (2 * fp >= n_frames)
+        return;
+    const long long fa = 2 * fp, fb = min(fa + 1, (long long)n_frames - 1);
+    const unsigned short* A  = static_cast<const unsigned short*>(p.in) + size_t(fa) * p.frame_px;
+    const unsigned short* Bf = static_cast<const unsigned short*>(p.in) + size_t(fb) * p.frame_px;
+    const int  u0 = gx * 4;
+    const int  v0 = strip * rows_per_strip, v1 = min(v0 + rows_per_strip, p.h);
+    constexpr bool R = feat_traits<FEAT>::right;
+    const bool use_f = IN == IN_U16_DEPTH;
+
+    curv_consts cc{1.f, 1.f};
+    if constexpr (FEAT == FEAT_CURVATURE && OUT == OUT_U16) {
+        cc.q_div = sub(p.hi, p.lo);
+        cc.q_rcp = rcp_refined(cc.q_div, mufu_rcp(cc.q_div));
+    }
+
+    wrow<FEAT> up, mid, dn;
+    commit<FEAT, IN>(load_raw<R>(p, A, Bf, v0 - 1, u0, use_f), up);
+    commit<FEAT, IN>(load_raw<R>(p, A, Bf, v0, u0, use_f), mid);
+    rawrow      raw = load_raw<R>(p, A, Bf, v0 + 1, u0, use_f);
+    rtabs<FEAT> tb  = load_tabs<FEAT>(p, v0, u0);
+    pos         at;
+    at.u0 = u0;
+    float col_in[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        col_in[i] = (u0 + i >= 1 && u0 + i < p.w - 1) ? 1.0f : 0.0f;
+#ifdef DC_ROT3
+    int v = v0;
+#define DC_STEP(UP, MID, DN)                                                   \
+    {                                                                          \
+        commit<FEAT, IN>(raw, DN);                                             \
+        raw  = load_raw<R>(p, A, Bf, v + 2, u0, use_f);                        \
+        tb   = load_tabs<FEAT>(p, v, u0);                                      \
+        at.v = v;                                                              \
+        at.oa = size_t(fa) * p.frame_px + size_t(v) * p.w + u0;                \
+        at.ob = size_t(fb) * p.frame_px + size_t(v) * p.w + u0;                \
+        for (int i = 0; i < 4; ++i)                                            \
+            at.inside[i] = col_in[i] * ((v >= 1 && v < p.h - 1) ? 1.0f : 0.0f); \
+        if constexpr (FEAT == FEAT_BEARING)                                    \
+            bearing_row<OUT>(p, UP, MID, DN, tb, at);                          \
+        else if constexpr (FEAT == FEAT_MAX_CURVE)                             \
+            max_curve_row<OUT>(p, UP, MID, DN, tb, at);                        \
+        else if constexpr (FEAT == FEAT_CURVATURE)                             \
+            curvature_row<OUT>(p, UP, MID, DN, tb, at, cc);                    \
+        if (++v >= v1)                                                         \
+            break;                                                             \
+    }
+    for (;;) {
+        DC_STEP(up, mid, dn)
+        DC_STEP(mid, dn, up)
+        DC_STEP(dn, up, mid)
+    }
+#undef DC_STEP
+#else
+#pragma unroll 1
+    for (int v = v0; v < v1; ++v) {
+        commit<FEAT, IN>(raw, dn);
+        raw                  = load_raw<R>(p, A, Bf, v + 2, u0, use_f);
+#ifdef DC_NO_TAB_PREFETCH
+        tb                   = load_tabs<FEAT>(p, v, u0);
+        const rtabs<FEAT> tn = tb;
+#else
+        const rtabs<FEAT> tn = load_tabs<FEAT>(p, v + 1, u0);
+#endif
+        at.v                 = v;
+        at.oa                = size_t(fa) * p.frame_px + size_t(v) * p.w + u0;
+        at.ob                = size_t(fb) * p.frame_px + size_t(v) * p.w + u0;
+        const float row_in   = (v >= 1 && v < p.h - 1) ? 1.0f : 0.0f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            at.inside[i] = col_in[i] * row_in;
+        if constexpr (FEAT == FEAT_BEARING)
+            bearing_row<OUT>(p, up, mid, dn, tb, at);
+        else if constexpr (FEAT == FEAT_MAX_CURVE)
+            max_curve_row<OUT>(p, up, mid, dn, tb, at);
+        else if constexpr (FEAT == FEAT_CURVATURE)
+            curvature_row<OUT>(p, up, mid, dn, tb, at, cc);
+        up  = mid;
+        mid = dn;
+        tb  = tn;
+    }
+#endif
+}
+
+}  // namespace pr
+}  // namespace dc
+#endif
