@@ -265,7 +265,8 @@ cudaError_t launch_pair(const dc::kparams& p, int n_frames, cudaStream_t s) {
     const long long blocks  = (threads + dc::pr::kPairThreads - 1) / dc::pr::kPairThreads;
     if (blocks > 0x7fffffffLL)
         return cudaErrorInvalidConfiguration;
-    dc::pr::pair_kernel<FEAT, IN, OUT><<<unsigned(blocks), dc::pr::kPairThreads, 0, s>>>(p, n_frames, rps);
+    dc::pr::pair_kernel<FEAT, IN, OUT>
+        <<<unsigned(blocks), dc::pr::kPairThreads, dc::pr::pair_smem_bytes<FEAT>(), s>>>(p, n_frames, rps);
     return cudaGetLastError();
 }
 

@@ -107,49 +107,85 @@ __device__ __forceinline__ f2 bearing2(f2 b, f2 c, f2 bb, f2 cc, f2 b2, float co
 }
 
 // ---------------------------------------------------------------------------
-// one input row of the two frames: columns u0-1 .. u0+4 as (A, B) pairs
+// Staging. Everything a thread needs for a later row (input pixels, range
+// factors, per-row camera tables) is fetched with cp.async into shared-memory
+// slots that belong to that thread alone, one row step ahead of its use:
+// the copies are in flight without holding registers (a register prefetch made
+// ptxas spill the freshly loaded values, stalling on them at once), the compiler
+// cannot sink them towards their use, and no barrier is needed because a thread
+// only reads back its own slots after cp.async.wait_group.
+// Slot s of stage g of thread t is the uint4 at smem[(g * NSLOT + s) * T + t]:
+// consecutive threads hit consecutive 16-byte words (conflict-free LDS.128).
+template <int BYTES>
+__device__ __forceinline__ void cp_async(void* smem_dst, const void* gsrc, bool pred) {
+    const unsigned d = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
+    const int      n = pred ? BYTES : 0;  // 0: nothing is read, the slot is zero-filled
+    asm volatile("cp.async.ca.shared.global [%0], [%1], %2, %3;" ::"r"(d), "l"(gsrc), "n"(BYTES),
+                 "r"(n)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+constexpr int kRawSlots = 4;
+// slot 0: 4 px of frame A | 4 px of frame B        (u16 x 8)
+// slot 1: the u16 pairs holding column u0-1 of A, of B, column u0+4 of A, of B
+// slot 2: range factor of the 4 columns            (f32 x 4)
+// slot 3: range factor of columns u0-1, u0+4       (f32 x 2)
+
+// one input row of the two frames: columns u0-1 .. u0+4
 struct rawrow {
     uint2    a, b;            // 4 u16 of frame A / B
-    unsigned la, lb, ra, rb;  // halo pixels (0 outside the image)
+    unsigned la, lb, ra, rb;  // words holding the halo pixels (0 outside the image):
+                              // left pixel in the HIGH half, right pixel in the LOW half
     float4   f;               // range factor of the 4 columns
     float    fl, fr;          // and of the halo columns
 };
 
 template <bool RIGHT>
-__device__ __forceinline__ rawrow load_raw(const kparams& p, const unsigned short* A,
-                                           const unsigned short* Bf, int r, int u0,
-                                           bool use_factor) {
-    rawrow x;
-    x.a = x.b = make_uint2(0u, 0u);
-    x.la = x.lb = x.ra = x.rb = 0u;
-    x.f                       = make_float4(1.f, 1.f, 1.f, 1.f);
-    x.fl = x.fr = 1.f;
-    if (r >= 0 && r < p.h) {
-        const size_t o = size_t(r) * p.w + u0;
-        x.a            = __ldg(reinterpret_cast<const uint2*>(A + o));
-        x.b            = __ldg(reinterpret_cast<const uint2*>(Bf + o));
-        const bool l = u0 > 0, rt = RIGHT && (u0 + 4 < p.w);
-        if (l) {
-            x.la = __ldg(A + o - 1);
-            x.lb = __ldg(Bf + o - 1);
-        }
-        if (rt) {
-            x.ra = __ldg(A + o + 4);
-            x.rb = __ldg(Bf + o + 4);
-        }
-        if (use_factor) {
-            if (p.range_factor.p == nullptr) {
-                x.f  = make_float4(p.range_factor.value, p.range_factor.value,
-                                   p.range_factor.value, p.range_factor.value);
-                x.fl = x.fr = p.range_factor.value;
-            } else {
-                x.f = __ldg(reinterpret_cast<const float4*>(p.range_factor.p + o));
-                if (l)
-                    x.fl = __ldg(p.range_factor.p + o - 1);
-                if (rt)
-                    x.fr = __ldg(p.range_factor.p + o + 4);
-            }
-        }
+__device__ __forceinline__ void issue_raw(const kparams& p, const unsigned short* A,
+                                          const unsigned short* Bf, int r, int u0,
+                                          bool use_factor, uint4* st, int stride) {
+    const bool   in = r >= 0 && r < p.h;
+    const size_t o  = size_t(in ? r : 0) * p.w + u0;
+    const bool   l = in && u0 > 0, rt = in && RIGHT && (u0 + 4 < p.w);
+    char*        s0 = reinterpret_cast<char*>(st);
+    char*        s1 = reinterpret_cast<char*>(st + stride);
+    cp_async<8>(s0, A + o, in);
+    cp_async<8>(s0 + 8, Bf + o, in);
+    cp_async<4>(s1, A + (l ? o - 2 : o), l);
+    cp_async<4>(s1 + 4, Bf + (l ? o - 2 : o), l);
+    if constexpr (RIGHT) {
+        cp_async<4>(s1 + 8, A + (rt ? o + 4 : o), rt);
+        cp_async<4>(s1 + 12, Bf + (rt ? o + 4 : o), rt);
+    }
+    if (use_factor && p.range_factor.p != nullptr) {
+        char*        s3 = reinterpret_cast<char*>(st + 3 * stride);
+        const float* f  = p.range_factor.p + o;
+        cp_async<16>(st + 2 * stride, f, in);
+        cp_async<4>(s3, l ? f - 1 : f, l);
+        if constexpr (RIGHT)
+            cp_async<4>(s3 + 4, rt ? f + 4 : f, rt);
+    }
+}
+
+template <bool RIGHT>
+__device__ __forceinline__ rawrow fetch_raw(const kparams& p, bool use_factor, const uint4* st,
+                                            int stride) {
+    rawrow      x;
+    const uint4 ab = st[0], hl = st[stride];
+    x.a            = make_uint2(ab.x, ab.y);
+    x.b            = make_uint2(ab.z, ab.w);
+    x.la = hl.x, x.lb = hl.y;
+    x.ra = RIGHT ? hl.z : 0u, x.rb = RIGHT ? hl.w : 0u;
+    if (use_factor && p.range_factor.p != nullptr) {
+        x.f             = *reinterpret_cast<const float4*>(st + 2 * stride);
+        const float4 fe = *reinterpret_cast<const float4*>(st + 3 * stride);
+        x.fl = fe.x, x.fr = fe.y;
+    } else {
+        const float v = use_factor ? p.range_factor.value : 1.0f;
+        x.f           = make_float4(v, v, v, v);
+        x.fl = x.fr = v;
     }
     return x;
 }
@@ -168,7 +204,7 @@ template <int IN, bool RIGHT>
 __device__ __forceinline__ void to_range(const rawrow& x, f2 (&rng)[6]) {
     const f2 m = B(-8388608.0f);
     f2       d[6];
-    d[0] = make_float2(magic_lo(x.la), magic_lo(x.lb));
+    d[0] = make_float2(magic_hi(x.la), magic_hi(x.lb));
     d[1] = make_float2(magic_lo(x.a.x), magic_lo(x.b.x));
     d[2] = make_float2(magic_hi(x.a.x), magic_hi(x.b.x));
     d[3] = make_float2(magic_lo(x.a.y), magic_lo(x.b.y));
@@ -212,14 +248,22 @@ __device__ __forceinline__ void store4(void* base, size_t oa, size_t ob, const f
     }
 }
 
-// table values of the 4 columns of row v (scalar when the table is uniform)
-__device__ __forceinline__ float4 tab4(const tab_ref& t, int w, int v, int u0) {
+// per-row camera table values: 4 columns -> one slot; uniform tables are
+// passed by value and need no copy
+__device__ __forceinline__ void issue_tab4(const tab_ref& t, int w, int v, int u0, bool in,
+                                           uint4* slot) {
+    if (t.p != nullptr)
+        cp_async<16>(slot, t.p + size_t(in ? v : 0) * w + u0, in);
+}
+__device__ __forceinline__ float4 fetch_tab4(const tab_ref& t, const uint4* slot) {
     if (t.p == nullptr)
         return make_float4(t.value, t.value, t.value, t.value);
-    return __ldg(reinterpret_cast<const float4*>(t.p + size_t(v) * w + u0));
+    return *reinterpret_cast<const float4*>(slot);
 }
-__device__ __forceinline__ float tab1(const tab_ref& t, int w, int v, int u) {
-    return t.p == nullptr ? t.value : __ldg(t.p + size_t(v) * w + u);
+__device__ __forceinline__ void issue_tab1(const tab_ref& t, int w, int v, int u, bool in,
+                                           void* dst) {
+    if (t.p != nullptr)
+        cp_async<4>(dst, t.p + (in ? size_t(v) * w + u : 0), in);
 }
 
 }  // namespace pr

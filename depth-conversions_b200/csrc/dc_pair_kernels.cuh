@@ -61,37 +61,69 @@ __device__ __forceinline__ void put4(float* d, float4 v) {
 }
 
 template <int FEAT>
-__device__ __forceinline__ rtabs<FEAT> load_tabs(const kparams& p, int v, int u0) {
-    rtabs<FEAT> t;
-    const int   w = p.w, h = p.h;
+struct tab_slots {
+    static constexpr int n = FEAT == FEAT_BEARING ? 4 : FEAT == FEAT_MAX_CURVE ? 7 : FEAT == FEAT_CURVATURE ? 3 : 0;
+};
+
+// Starts the copies of the camera tables row `v` of the feature needs into the
+// thread's table slots st[0], st[stride], ...
+template <int FEAT>
+__device__ __forceinline__ void issue_tabs(const kparams& p, int v, int u0, uint4* st, int stride) {
+    const int w = p.w, h = p.h;
     if constexpr (FEAT == FEAT_BEARING) {
         const bool in = v >= 0 && v < h;
 #pragma unroll
         for (int d = 0; d < 4; ++d)
-            t.c[d] = (in && p.out[d] != nullptr) ? tab4(p.cosp[d], w, v, u0)
-                                                 : make_float4(.5f, .5f, .5f, .5f);
+            if (p.out[d] != nullptr)
+                issue_tab4(p.cosp[d], w, v, u0, in, st + d * stride);
     } else if constexpr (FEAT == FEAT_MAX_CURVE) {
         // depth_to_max_curve.h:113-139: all eight phi() are angles between a
-        // pixel and one of its bearing "prior" neighbours (see dc_kernels.cuh)
-        const bool  in   = v >= 1 && v < h - 1;
-        const bool  more = u0 + 4 < w;
-        const float dflt = 0.5f;
-        float4      f    = make_float4(dflt, dflt, dflt, dflt);
-        put4(t.cH, in ? tab4(p.cosp[0], w, v, u0) : f);
-        t.cH[4] = (in && more) ? tab1(p.cosp[0], w, v, u0 + 4) : dflt;
-        put4(t.cV0, in ? tab4(p.cosp[1], w, v, u0) : f);
-        put4(t.cV1, in ? tab4(p.cosp[1], w, v + 1, u0) : f);
-        put4(t.cD0, in ? tab4(p.cosp[2], w, v, u0) : f);
-        put4(t.cD1, in ? tab4(p.cosp[2], w, v + 1, u0) : f);
-        t.cD1[4] = (in && more) ? tab1(p.cosp[2], w, v + 1, u0 + 4) : dflt;
-        put4(t.cA, in ? tab4(p.cosp[3], w, v - 1, u0) : f);
-        t.cA[4] = (in && more) ? tab1(p.cosp[3], w, v - 1, u0 + 4) : dflt;
+        // pixel and one of its bearing "prior" neighbours (see dc_kernels.cuh):
+        //   hor1 = H(u,v)      hor2 = H(u+1,v)      ver1 = V(u,v)   ver2 = V(u,v+1)
+        //   dia1 = D(u,v)      dia2 = D(u+1,v+1)
+        //   ant1 = phi((u+1,v+1),(u,v)) = D(u+1,v+1) (sic, :136)   ant2 = A(u+1,v-1)
+        const bool in = v >= 1 && v < h - 1, more = in && u0 + 4 < w;
+        issue_tab4(p.cosp[0], w, v, u0, in, st);
+        issue_tab4(p.cosp[1], w, v, u0, in, st + stride);
+        issue_tab4(p.cosp[1], w, v + 1, u0, in, st + 2 * stride);
+        issue_tab4(p.cosp[2], w, v, u0, in, st + 3 * stride);
+        issue_tab4(p.cosp[2], w, v + 1, u0, in, st + 4 * stride);
+        issue_tab4(p.cosp[3], w, v - 1, u0, in, st + 5 * stride);
+        char* e = reinterpret_cast<char*>(st + 6 * stride);
+        issue_tab1(p.cosp[0], w, v, u0 + 4, more, e);
+        issue_tab1(p.cosp[2], w, v + 1, u0 + 4, more, e + 4);
+        issue_tab1(p.cosp[3], w, v - 1, u0 + 4, more, e + 8);
     } else if constexpr (FEAT == FEAT_CURVATURE) {
-        const bool   in = v >= 1 && v < h - 1;
-        const float4 f  = make_float4(1.f, 1.f, 1.f, 1.f);
-        t.phi           = in ? tab4(p.d_phi, w, v, u0) : f;
-        t.theta         = in ? tab4(p.d_theta, w, v, u0) : f;
-        t.pt            = in ? tab4(p.d_phi_theta, w, v, u0) : f;
+        const bool in = v >= 1 && v < h - 1;
+        issue_tab4(p.d_phi, w, v, u0, in, st);
+        issue_tab4(p.d_theta, w, v, u0, in, st + stride);
+        issue_tab4(p.d_phi_theta, w, v, u0, in, st + 2 * stride);
+    }
+}
+
+template <int FEAT>
+__device__ __forceinline__ rtabs<FEAT> fetch_tabs(const kparams& p, const uint4* st, int stride) {
+    rtabs<FEAT> t;
+    if constexpr (FEAT == FEAT_BEARING) {
+#pragma unroll
+        for (int d = 0; d < 4; ++d)
+            t.c[d] = p.out[d] != nullptr ? fetch_tab4(p.cosp[d], st + d * stride)
+                                         : make_float4(.5f, .5f, .5f, .5f);
+    } else if constexpr (FEAT == FEAT_MAX_CURVE) {
+        put4(t.cH, fetch_tab4(p.cosp[0], st));
+        put4(t.cV0, fetch_tab4(p.cosp[1], st + stride));
+        put4(t.cV1, fetch_tab4(p.cosp[1], st + 2 * stride));
+        put4(t.cD0, fetch_tab4(p.cosp[2], st + 3 * stride));
+        put4(t.cD1, fetch_tab4(p.cosp[2], st + 4 * stride));
+        put4(t.cA, fetch_tab4(p.cosp[3], st + 5 * stride));
+        const float4 e = *reinterpret_cast<const float4*>(st + 6 * stride);
+        t.cH[4]        = p.cosp[0].p != nullptr ? e.x : p.cosp[0].value;
+        t.cD1[4]       = p.cosp[2].p != nullptr ? e.y : p.cosp[2].value;
+        t.cA[4]        = p.cosp[3].p != nullptr ? e.z : p.cosp[3].value;
+    } else if constexpr (FEAT == FEAT_CURVATURE) {
+        t.phi   = fetch_tab4(p.d_phi, st);
+        t.theta = fetch_tab4(p.d_theta, st + stride);
+        t.pt    = fetch_tab4(p.d_phi_theta, st + 2 * stride);
     }
     return t;
 }
@@ -291,8 +323,13 @@ constexpr int min_blocks() {
 #ifdef DC_MIN_BLOCKS
     return DC_MIN_BLOCKS;
 #else
-    return FEAT == FEAT_BEARING ? 5 : 4;
+    return 4;
 #endif
+}
+
+template <int FEAT>
+constexpr size_t pair_smem_bytes() {
+    return size_t(2) * (kRawSlots + tab_slots<FEAT>::n) * kPairThreads * sizeof(uint4);
 }
 
 template <int FEAT, int IN, int OUT>
@@ -321,59 +358,46 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT>())
         cc.q_rcp = rcp_refined(cc.q_div, mufu_rcp(cc.q_div));
     }
 
+    // ---- staging slots of this thread (dc_pair.cuh "Staging") ----
+    extern __shared__ uint4 smem[];
+    constexpr int NSLOT = kRawSlots + tab_slots<FEAT>::n;
+    constexpr int T     = kPairThreads;
+    uint4* const  stg0  = smem + threadIdx.x;
+    uint4* const  stg1  = smem + NSLOT * T + threadIdx.x;
+
     wrow<FEAT> up, mid, dn;
-    commit<FEAT, IN>(load_raw<R>(p, A, Bf, v0 - 1, u0, use_f), up);
-    commit<FEAT, IN>(load_raw<R>(p, A, Bf, v0, u0, use_f), mid);
-    rawrow      raw = load_raw<R>(p, A, Bf, v0 + 1, u0, use_f);
-    rtabs<FEAT> tb  = load_tabs<FEAT>(p, v0, u0);
-    pos         at;
+    issue_raw<R>(p, A, Bf, v0 - 1, u0, use_f, stg0, T);
+    issue_raw<R>(p, A, Bf, v0, u0, use_f, stg1, T);
+    cp_async_commit();
+    cp_async_wait_all();
+    commit<FEAT, IN>(fetch_raw<R>(p, use_f, stg0, T), up);
+    commit<FEAT, IN>(fetch_raw<R>(p, use_f, stg1, T), mid);
+    issue_raw<R>(p, A, Bf, v0 + 1, u0, use_f, stg0, T);
+    issue_tabs<FEAT>(p, v0, u0, stg0 + kRawSlots * T, T);
+    cp_async_commit();
+
+    pos at;
     at.u0 = u0;
     float col_in[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
         col_in[i] = (u0 + i >= 1 && u0 + i < p.w - 1) ? 1.0f : 0.0f;
-#ifdef DC_ROT3
-    int v = v0;
-#define DC_STEP(UP, MID, DN)                                                   \
-    {                                                                          \
-        commit<FEAT, IN>(raw, DN);                                             \
-        raw  = load_raw<R>(p, A, Bf, v + 2, u0, use_f);                        \
-        tb   = load_tabs<FEAT>(p, v, u0);                                      \
-        at.v = v;                                                              \
-        at.oa = size_t(fa) * p.frame_px + size_t(v) * p.w + u0;                \
-        at.ob = size_t(fb) * p.frame_px + size_t(v) * p.w + u0;                \
-        for (int i = 0; i < 4; ++i)                                            \
-            at.inside[i] = col_in[i] * ((v >= 1 && v < p.h - 1) ? 1.0f : 0.0f); \
-        if constexpr (FEAT == FEAT_BEARING)                                    \
-            bearing_row<OUT>(p, UP, MID, DN, tb, at);                          \
-        else if constexpr (FEAT == FEAT_MAX_CURVE)                             \
-            max_curve_row<OUT>(p, UP, MID, DN, tb, at);                        \
-        else if constexpr (FEAT == FEAT_CURVATURE)                             \
-            curvature_row<OUT>(p, UP, MID, DN, tb, at, cc);                    \
-        if (++v >= v1)                                                         \
-            break;                                                             \
-    }
-    for (;;) {
-        DC_STEP(up, mid, dn)
-        DC_STEP(mid, dn, up)
-        DC_STEP(dn, up, mid)
-    }
-#undef DC_STEP
-#else
+    int cur = 0;
 #pragma unroll 1
     for (int v = v0; v < v1; ++v) {
-        commit<FEAT, IN>(raw, dn);
-        raw                  = load_raw<R>(p, A, Bf, v + 2, u0, use_f);
-#ifdef DC_NO_TAB_PREFETCH
-        tb                   = load_tabs<FEAT>(p, v, u0);
-        const rtabs<FEAT> tn = tb;
-#else
-        const rtabs<FEAT> tn = load_tabs<FEAT>(p, v + 1, u0);
-#endif
-        at.v                 = v;
-        at.oa                = size_t(fa) * p.frame_px + size_t(v) * p.w + u0;
-        at.ob                = size_t(fb) * p.frame_px + size_t(v) * p.w + u0;
-        const float row_in   = (v >= 1 && v < p.h - 1) ? 1.0f : 0.0f;
+        uint4* const sc = cur ? stg1 : stg0;  // row v+1 and the tables of row v
+        uint4* const sn = cur ? stg0 : stg1;
+        cur ^= 1;
+        cp_async_wait_all();
+        commit<FEAT, IN>(fetch_raw<R>(p, use_f, sc, T), dn);
+        const rtabs<FEAT> tb = fetch_tabs<FEAT>(p, sc + kRawSlots * T, T);
+        issue_raw<R>(p, A, Bf, v + 2, u0, use_f, sn, T);
+        issue_tabs<FEAT>(p, v + 1, u0, sn + kRawSlots * T, T);
+        cp_async_commit();
+        at.v               = v;
+        at.oa              = size_t(fa) * p.frame_px + size_t(v) * p.w + u0;
+        at.ob              = size_t(fb) * p.frame_px + size_t(v) * p.w + u0;
+        const float row_in = (v >= 1 && v < p.h - 1) ? 1.0f : 0.0f;
 #pragma unroll
         for (int i = 0; i < 4; ++i)
             at.inside[i] = col_in[i] * row_in;
@@ -385,9 +409,8 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT>())
             curvature_row<OUT>(p, up, mid, dn, tb, at, cc);
         up  = mid;
         mid = dn;
-        tb  = tn;
     }
-#endif
+    cp_async_wait_all();
 }
 
 }  // namespace pr
