@@ -72,10 +72,11 @@ __device__ __forceinline__ f2 div2(f2 a, f2 b, f2 y) {
 }
 __device__ __forceinline__ f2 div2_fast(f2 a, f2 b) { return div2(a, b, rcp_refine2(b, rcp2(b))); }
 
-// acos(clamp(q, -1 + delta, 1 - delta)), relative error < 1.2e-6:
-// sqrt(1 - a) * P5(a), a = min(|q|, 1 - delta), reflected for q < 0.
-// A NaN q (only on lanes that are masked out afterwards) comes out finite.
-__device__ __forceinline__ f2 acos2(f2 q) {
+// acos(min(|q|, 1 - delta)), relative error < 1.2e-6: sqrt(1 - a) * P5(a).
+// The caller reflects for q < 0 (acos(q) = pi - acos(|q|)); together that is
+// acos(clamp(q, -1 + delta, 1 - delta)) of math/triangles.h:55-58. A NaN q
+// (only on lanes that are masked out afterwards) comes out finite.
+__device__ __forceinline__ f2 acos_abs2(f2 q) {
     const f2 a = make_float2(fminf(fabsf(q.x), DC_ONE_MINUS_DELTA),
                              fminf(fabsf(q.y), DC_ONE_MINUS_DELTA));
     const f2 t = sub2(B(1.0f), a);
@@ -85,25 +86,38 @@ __device__ __forceinline__ f2 acos2(f2 q) {
     p          = fma2(p, a, B(0.08785323798656464f));
     p          = fma2(p, a, B(-0.2145095020532608f));
     p          = fma2(p, a, B(1.5707951784133911f));
-    const f2 r = mul2(s, p);
-    const f2 m = sub2(B(3.14159274101257324f), r);
+    return mul2(s, p);
+}
+#define DC_PI_F 3.14159274101257324f
+__device__ __forceinline__ f2 reflect2(f2 r, f2 q) {
+    const f2 m = sub2(B(DC_PI_F), r);
     return make_float2(q.x < 0.0f ? m.x : r.x, q.y < 0.0f ? m.y : r.y);
 }
 
 // math/triangles.h:27-64 for both frames: b, c the two ranges, bb / cc their
-// squares, b2 = 2b, cosine of the (camera-only) ray angle broadcast.
-// b2c = (2b)*c is handed back for the "either depth is zero" test.
-__device__ __forceinline__ f2 bearing2(f2 b, f2 c, f2 bb, f2 cc, f2 b2, float cos_alpha,
-                                       f2& b2c) {
+// squares, cosine of the (camera-only) ray angle broadcast.
+//   nom = b - c*cos;  rad = (bb + cc) - ((2b)*c)*cos;  q = nom / sqrt(rad)
+// (2b)*c = 2*RN(b*c) and (..)*cos = 2*RN(RN(b*c)*cos) exactly (scaling by two
+// commutes with rounding), so rad = RN(sum - 2t) is one FFMA2 with t = RN(bc*cos).
+// bc = b*c is handed back for the "either depth is zero" test ((2b)*c == 0).
+struct bres {
+    f2 r;   // acos(min(|q|, 1 - delta))
+    f2 q;   // the ratio: its sign selects the reflection
+    f2 bc;  // b * c
+};
+__device__ __forceinline__ bres bearing_core2(f2 b, f2 c, f2 bb, f2 cc, float cos_alpha) {
+    bres     o;
     const f2 ca  = B(cos_alpha);
     const f2 nom = sub2(b, mul2(c, ca));
     const f2 sum = add2(bb, cc);
-    b2c          = mul2(b2, c);
-    const f2 rad = sub2(sum, mul2(b2c, ca));
+    o.bc         = mul2(b, c);
+    const f2 t   = mul2(o.bc, ca);
+    const f2 rad = fma2(B(-2.0f), t, sum);
     f2       y;
     const f2 d = sqrt2(rad, y);
-    const f2 q = div2(nom, d, rcp_refine2(d, y));
-    return acos2(q);
+    o.q        = div2(nom, d, rcp_refine2(d, y));
+    o.r        = acos_abs2(o.q);
+    return o;
 }
 
 // ---------------------------------------------------------------------------
@@ -142,35 +156,46 @@ struct rawrow {
     float    fl, fr;          // and of the halo columns
 };
 
+// Per-thread constants of the marching loop: every stream as a pointer to the
+// thread's first column, so that a row is reached by adding one 32-bit row
+// offset; the halo predicates / offsets do not change from row to row.
+struct lane {
+    const unsigned short *A, *Bf;  // frames A and B at column u0
+    const float*          fac;     // range factor table at column u0 (or nullptr)
+    int                   offl, offr;  // element offset of the word holding u0-1 / u0+4
+    bool                  hl, hr;      // halo column inside the image
+};
+
+// Starts the copies of input row `roff / w` (roff = row * w, row clamped into
+// the image; `in` false = outside: zero-fill) into raw slots st[0..3*stride].
 template <bool RIGHT>
-__device__ __forceinline__ void issue_raw(const kparams& p, const unsigned short* A,
-                                          const unsigned short* Bf, int r, int u0,
-                                          bool use_factor, uint4* st, int stride) {
-    const bool   in = r >= 0 && r < p.h;
-    const size_t o  = size_t(in ? r : 0) * p.w + u0;
-    const bool   l = in && u0 > 0, rt = in && RIGHT && (u0 + 4 < p.w);
-    char*        s0 = reinterpret_cast<char*>(st);
-    char*        s1 = reinterpret_cast<char*>(st + stride);
-    cp_async<8>(s0, A + o, in);
-    cp_async<8>(s0 + 8, Bf + o, in);
-    cp_async<4>(s1, A + (l ? o - 2 : o), l);
-    cp_async<4>(s1 + 4, Bf + (l ? o - 2 : o), l);
+__device__ __forceinline__ void issue_raw(const lane& L, int roff, bool in, uint4* st,
+                                          int stride) {
+    const bool l = in && L.hl, rt = in && L.hr;
+    char*      s0 = reinterpret_cast<char*>(st);
+    char*      s1 = reinterpret_cast<char*>(st + stride);
+    const unsigned short* a = L.A + roff;
+    const unsigned short* b = L.Bf + roff;
+    cp_async<8>(s0, a, in);
+    cp_async<8>(s0 + 8, b, in);
+    cp_async<4>(s1, a + L.offl, l);
+    cp_async<4>(s1 + 4, b + L.offl, l);
     if constexpr (RIGHT) {
-        cp_async<4>(s1 + 8, A + (rt ? o + 4 : o), rt);
-        cp_async<4>(s1 + 12, Bf + (rt ? o + 4 : o), rt);
+        cp_async<4>(s1 + 8, a + L.offr, rt);
+        cp_async<4>(s1 + 12, b + L.offr, rt);
     }
-    if (use_factor && p.range_factor.p != nullptr) {
+    if (L.fac != nullptr) {
         char*        s3 = reinterpret_cast<char*>(st + 3 * stride);
-        const float* f  = p.range_factor.p + o;
+        const float* f  = L.fac + roff;
         cp_async<16>(st + 2 * stride, f, in);
-        cp_async<4>(s3, l ? f - 1 : f, l);
+        cp_async<4>(s3, f + (L.hl ? -1 : 0), l);
         if constexpr (RIGHT)
-            cp_async<4>(s3 + 4, rt ? f + 4 : f, rt);
+            cp_async<4>(s3 + 4, f + L.offr, rt);
     }
 }
 
 template <bool RIGHT>
-__device__ __forceinline__ rawrow fetch_raw(const kparams& p, bool use_factor, const uint4* st,
+__device__ __forceinline__ rawrow fetch_raw(const lane& L, float uniform_factor, const uint4* st,
                                             int stride) {
     rawrow      x;
     const uint4 ab = st[0], hl = st[stride];
@@ -178,12 +203,12 @@ __device__ __forceinline__ rawrow fetch_raw(const kparams& p, bool use_factor, c
     x.b            = make_uint2(ab.z, ab.w);
     x.la = hl.x, x.lb = hl.y;
     x.ra = RIGHT ? hl.z : 0u, x.rb = RIGHT ? hl.w : 0u;
-    if (use_factor && p.range_factor.p != nullptr) {
+    if (L.fac != nullptr) {
         x.f             = *reinterpret_cast<const float4*>(st + 2 * stride);
         const float4 fe = *reinterpret_cast<const float4*>(st + 3 * stride);
         x.fl = fe.x, x.fr = fe.y;
     } else {
-        const float v = use_factor ? p.range_factor.value : 1.0f;
+        const float v = uniform_factor;
         x.f           = make_float4(v, v, v, v);
         x.fl = x.fr = v;
     }
@@ -229,6 +254,14 @@ __device__ __forceinline__ uint2 pack4(float a0, float a1, float a2, float a3) {
                       __byte_perm(__float_as_uint(a2), __float_as_uint(a3), 0x5410));
 }
 
+// Stores 4 u16 pixels per frame from floats that already hold 1.5*2^23 + value
+// (the integer sits in the low mantissa bits).
+__device__ __forceinline__ void store4_magic(void* base, size_t oa, size_t ob, const f2 (&s)[4]) {
+    unsigned short* o = static_cast<unsigned short*>(base);
+    *reinterpret_cast<uint2*>(o + oa) = pack4(s[0].x, s[1].x, s[2].x, s[3].x);
+    *reinterpret_cast<uint2*>(o + ob) = pack4(s[0].y, s[1].y, s[2].y, s[3].y);
+}
+
 // Stores 4 pixels of frame A (.x halves) and frame B (.y halves).
 // OUT_U16: v already holds value * scale; round half to even by the magic add.
 template <int OUT>
@@ -249,21 +282,19 @@ __device__ __forceinline__ void store4(void* base, size_t oa, size_t ob, const f
 }
 
 // per-row camera table values: 4 columns -> one slot; uniform tables are
-// passed by value and need no copy
-__device__ __forceinline__ void issue_tab4(const tab_ref& t, int w, int v, int u0, bool in,
-                                           uint4* slot) {
+// passed by value and need no copy. `off` = row * w + u0 (clamped into the table).
+__device__ __forceinline__ void issue_tab4(const tab_ref& t, int off, bool in, uint4* slot) {
     if (t.p != nullptr)
-        cp_async<16>(slot, t.p + size_t(in ? v : 0) * w + u0, in);
+        cp_async<16>(slot, t.p + off, in);
 }
 __device__ __forceinline__ float4 fetch_tab4(const tab_ref& t, const uint4* slot) {
     if (t.p == nullptr)
         return make_float4(t.value, t.value, t.value, t.value);
     return *reinterpret_cast<const float4*>(slot);
 }
-__device__ __forceinline__ void issue_tab1(const tab_ref& t, int w, int v, int u, bool in,
-                                           void* dst) {
+__device__ __forceinline__ void issue_tab1(const tab_ref& t, int off, bool in, void* dst) {
     if (t.p != nullptr)
-        cp_async<4>(dst, t.p + (in ? size_t(v) * w + u : 0), in);
+        cp_async<4>(dst, t.p + off, in);
 }
 
 }  // namespace pr

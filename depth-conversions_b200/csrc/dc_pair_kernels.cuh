@@ -65,17 +65,19 @@ struct tab_slots {
     static constexpr int n = FEAT == FEAT_BEARING ? 4 : FEAT == FEAT_MAX_CURVE ? 7 : FEAT == FEAT_CURVATURE ? 3 : 0;
 };
 
-// Starts the copies of the camera tables row `v` of the feature needs into the
-// thread's table slots st[0], st[stride], ...
+// Starts the copies of the camera tables that row `v` of the feature needs
+// into the thread's table slots st[0], st[stride], ... `off` = v * w + u0.
 template <int FEAT>
-__device__ __forceinline__ void issue_tabs(const kparams& p, int v, int u0, uint4* st, int stride) {
+__device__ __forceinline__ void issue_tabs(const kparams& p, int v, int off, int u0, uint4* st,
+                                           int stride) {
     const int w = p.w, h = p.h;
     if constexpr (FEAT == FEAT_BEARING) {
-        const bool in = v >= 0 && v < h;
+        const bool in = v < h;
+        off           = in ? off : 0;
 #pragma unroll
         for (int d = 0; d < 4; ++d)
             if (p.out[d] != nullptr)
-                issue_tab4(p.cosp[d], w, v, u0, in, st + d * stride);
+                issue_tab4(p.cosp[d], off, in, st + d * stride);
     } else if constexpr (FEAT == FEAT_MAX_CURVE) {
         // depth_to_max_curve.h:113-139: all eight phi() are angles between a
         // pixel and one of its bearing "prior" neighbours (see dc_kernels.cuh):
@@ -83,21 +85,24 @@ __device__ __forceinline__ void issue_tabs(const kparams& p, int v, int u0, uint
         //   dia1 = D(u,v)      dia2 = D(u+1,v+1)
         //   ant1 = phi((u+1,v+1),(u,v)) = D(u+1,v+1) (sic, :136)   ant2 = A(u+1,v-1)
         const bool in = v >= 1 && v < h - 1, more = in && u0 + 4 < w;
-        issue_tab4(p.cosp[0], w, v, u0, in, st);
-        issue_tab4(p.cosp[1], w, v, u0, in, st + stride);
-        issue_tab4(p.cosp[1], w, v + 1, u0, in, st + 2 * stride);
-        issue_tab4(p.cosp[2], w, v, u0, in, st + 3 * stride);
-        issue_tab4(p.cosp[2], w, v + 1, u0, in, st + 4 * stride);
-        issue_tab4(p.cosp[3], w, v - 1, u0, in, st + 5 * stride);
-        char* e = reinterpret_cast<char*>(st + 6 * stride);
-        issue_tab1(p.cosp[0], w, v, u0 + 4, more, e);
-        issue_tab1(p.cosp[2], w, v + 1, u0 + 4, more, e + 4);
-        issue_tab1(p.cosp[3], w, v - 1, u0 + 4, more, e + 8);
+        off           = in ? off : w;  // rows off-w .. off+w stay inside the table
+        issue_tab4(p.cosp[0], off, in, st);
+        issue_tab4(p.cosp[1], off, in, st + stride);
+        issue_tab4(p.cosp[1], off + w, in, st + 2 * stride);
+        issue_tab4(p.cosp[2], off, in, st + 3 * stride);
+        issue_tab4(p.cosp[2], off + w, in, st + 4 * stride);
+        issue_tab4(p.cosp[3], off - w, in, st + 5 * stride);
+        char*     e  = reinterpret_cast<char*>(st + 6 * stride);
+        const int o4 = more ? 4 : 0;
+        issue_tab1(p.cosp[0], off + o4, more, e);
+        issue_tab1(p.cosp[2], off + w + o4, more, e + 4);
+        issue_tab1(p.cosp[3], off - w + o4, more, e + 8);
     } else if constexpr (FEAT == FEAT_CURVATURE) {
         const bool in = v >= 1 && v < h - 1;
-        issue_tab4(p.d_phi, w, v, u0, in, st);
-        issue_tab4(p.d_theta, w, v, u0, in, st + stride);
-        issue_tab4(p.d_phi_theta, w, v, u0, in, st + 2 * stride);
+        off           = in ? off : 0;
+        issue_tab4(p.d_phi, off, in, st);
+        issue_tab4(p.d_theta, off, in, st + stride);
+        issue_tab4(p.d_phi_theta, off, in, st + 2 * stride);
     }
 }
 
@@ -134,14 +139,10 @@ __device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BE
                                             const wrow<FEAT_BEARING>& mid,
                                             const wrow<FEAT_BEARING>& dn,
                                             const rtabs<FEAT_BEARING>& tb, const pos& at) {
-    f2 su[5], sm[5], sd[4];
+    f2 sm[5];  // squares of the centre row: b*b of every pixel, c*c for horizontal
 #pragma unroll
-    for (int i = 0; i < 5; ++i) {
-        su[i] = mul2(up.r[i], up.r[i]);
+    for (int i = 0; i < 5; ++i)
         sm[i] = mul2(mid.r[i], mid.r[i]);
-        if (i < 4)
-            sd[i] = mul2(dn.r[i], dn.r[i]);
-    }
 #pragma unroll
     for (int d = 0; d < 4; ++d) {
         if (p.out[d] == nullptr)
@@ -151,19 +152,35 @@ __device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BE
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const f2 b = mid.r[i + 1], bb = sm[i + 1];
-            const f2 b2 = add2(b, b);
             // prior pixel: hor (u-1,v), ver (u,v-1), dia (u-1,v-1), anti (u-1,v+1)
-            const f2 c  = d == 0 ? mid.r[i] : d == 1 ? up.r[i + 1] : d == 2 ? up.r[i] : dn.r[i];
-            const f2 cc = d == 0 ? sm[i] : d == 1 ? su[i + 1] : d == 2 ? su[i] : sd[i];
-            f2       b2c;
-            f2       a = bearing2(b, c, bb, cc, b2, cs[i], b2c);
+            const f2   c  = d == 0 ? mid.r[i] : d == 1 ? up.r[i + 1] : d == 2 ? up.r[i] : dn.r[i];
+            const f2   cc = d == 0 ? sm[i] : mul2(c, c);
+            const bres k  = bearing_core2(b, c, bb, cc, cs[i]);
             // depth_to_bearing.h:204-207: either depth 0 (or the prior pixel
             // outside the image, which reads as 0) -> 0
-            a.x  = b2c.x != 0.0f ? a.x : 0.0f;
-            a.y  = b2c.y != 0.0f ? a.y : 0.0f;
-            o[i] = OUT == OUT_U16 ? mul2(a, B(p.q_bearing)) : a;
+            const bool va = k.bc.x != 0.0f, vb = k.bc.y != 0.0f;
+            if constexpr (OUT == OUT_U16) {
+                // convert_bearing (:282-301): round(angle * 65535/pi). Reflection,
+                // scale and the round-half-even magic constant in ONE FFMA2:
+                // (pi - r) * Q + M = r * (-Q) + (pi*Q + M). Against scaling first
+                // and rounding afterwards this moves a result by at most one LSB
+                // (tolerance of the quantised images: +-1 LSB; acos itself is
+                // only 1e-6 accurate against glibc).
+                const float Q = p.q_bearing, M = 12582912.0f, C = fmaf(DC_PI_F, Q, M);
+                const bool  na = k.q.x < 0.0f, nb = k.q.y < 0.0f;
+                const f2    sq  = make_float2(na ? -Q : Q, nb ? -Q : Q);
+                const f2    off = make_float2(na ? C : M, nb ? C : M);
+                const f2    x   = fma2(k.r, sq, off);
+                o[i]            = make_float2(va ? x.x : M, vb ? x.y : M);
+            } else {
+                const f2 a = reflect2(k.r, k.q);
+                o[i]       = make_float2(va ? a.x : 0.0f, vb ? a.y : 0.0f);
+            }
         }
-        store4<OUT>(p.out[d], at.oa, at.ob, o);
+        if constexpr (OUT == OUT_U16)
+            store4_magic(p.out[d], at.oa, at.ob, o);
+        else
+            store4<OUT>(p.out[d], at.oa, at.ob, o);
     }
 }
 
@@ -184,16 +201,15 @@ __device__ __forceinline__ void max_curve_row(const kparams& p, const wrow<FEAT_
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         const int c  = i + 1;
-        const f2  d0 = mid.r[c], bb = sm[c], b2 = add2(d0, d0);
+        const f2  d0 = mid.r[c], bb = sm[c];
         // angle_formula (:55-82): 0 if any of the three depths is 0, else the
         // sum of the two bearing angles
         auto pair = [&](f2 dm, f2 smm, f2 dp, f2 spp, float c1, float c2) {
-            f2       x1, x2;
-            const f2 a1 = bearing2(d0, dm, bb, smm, b2, c1, x1);
-            const f2 a2 = bearing2(d0, dp, bb, spp, b2, c2, x2);
-            const f2 s  = add2(a1, a2);
-            return make_float2((x1.x != 0.0f && x2.x != 0.0f) ? s.x : 0.0f,
-                               (x1.y != 0.0f && x2.y != 0.0f) ? s.y : 0.0f);
+            const bres k1 = bearing_core2(d0, dm, bb, smm, c1);
+            const bres k2 = bearing_core2(d0, dp, bb, spp, c2);
+            const f2   s  = add2(reflect2(k1.r, k1.q), reflect2(k2.r, k2.q));
+            return make_float2((k1.bc.x != 0.0f && k2.bc.x != 0.0f) ? s.x : 0.0f,
+                               (k1.bc.y != 0.0f && k2.bc.y != 0.0f) ? s.y : 0.0f);
         };
         const f2 ah = pair(mid.r[c - 1], sm[c - 1], mid.r[c + 1], sm[c + 1], tb.cH[i], tb.cH[i + 1]);
         const f2 av = pair(up.r[c], su[c], dn.r[c], sd[c], tb.cV0[i], tb.cV1[i]);
@@ -345,12 +361,18 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT>())
     if (2 * fp >= n_frames)
         return;
     const long long fa = 2 * fp, fb = min(fa + 1, (long long)n_frames - 1);
-    const unsigned short* A  = static_cast<const unsigned short*>(p.in) + size_t(fa) * p.frame_px;
-    const unsigned short* Bf = static_cast<const unsigned short*>(p.in) + size_t(fb) * p.frame_px;
-    const int  u0 = gx * 4;
-    const int  v0 = strip * rows_per_strip, v1 = min(v0 + rows_per_strip, p.h);
+    const int  u0 = gx * 4, w = p.w, h = p.h;
+    const int  v0 = strip * rows_per_strip, v1 = min(v0 + rows_per_strip, h);
     constexpr bool R = feat_traits<FEAT>::right;
-    const bool use_f = IN == IN_U16_DEPTH;
+    lane L;
+    L.A   = static_cast<const unsigned short*>(p.in) + size_t(fa) * p.frame_px + u0;
+    L.Bf  = static_cast<const unsigned short*>(p.in) + size_t(fb) * p.frame_px + u0;
+    L.fac = (IN == IN_U16_DEPTH && p.range_factor.p != nullptr) ? p.range_factor.p + u0 : nullptr;
+    L.hl  = u0 > 0;
+    L.hr  = R && (u0 + 4 < w);
+    L.offl = L.hl ? -2 : 0;
+    L.offr = L.hr ? 4 : 0;
+    const float ufac = IN == IN_U16_DEPTH ? p.range_factor.value : 1.0f;
 
     curv_consts cc{1.f, 1.f};
     if constexpr (FEAT == FEAT_CURVATURE && OUT == OUT_U16) {
@@ -366,38 +388,42 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT>())
     uint4* const  stg1  = smem + NSLOT * T + threadIdx.x;
 
     wrow<FEAT> up, mid, dn;
-    issue_raw<R>(p, A, Bf, v0 - 1, u0, use_f, stg0, T);
-    issue_raw<R>(p, A, Bf, v0, u0, use_f, stg1, T);
+    issue_raw<R>(L, max(v0 - 1, 0) * w, v0 >= 1, stg0, T);
+    issue_raw<R>(L, v0 * w, true, stg1, T);
     cp_async_commit();
     cp_async_wait_all();
-    commit<FEAT, IN>(fetch_raw<R>(p, use_f, stg0, T), up);
-    commit<FEAT, IN>(fetch_raw<R>(p, use_f, stg1, T), mid);
-    issue_raw<R>(p, A, Bf, v0 + 1, u0, use_f, stg0, T);
-    issue_tabs<FEAT>(p, v0, u0, stg0 + kRawSlots * T, T);
+    commit<FEAT, IN>(fetch_raw<R>(L, ufac, stg0, T), up);
+    commit<FEAT, IN>(fetch_raw<R>(L, ufac, stg1, T), mid);
+    issue_raw<R>(L, min(v0 + 1, h - 1) * w, v0 + 1 < h, stg0, T);
+    issue_tabs<FEAT>(p, v0, v0 * w + u0, u0, stg0 + kRawSlots * T, T);
     cp_async_commit();
 
     pos at;
     at.u0 = u0;
+    at.oa = size_t(fa) * p.frame_px + size_t(v0) * w + u0;
+    at.ob = size_t(fb) * p.frame_px + size_t(v0) * w + u0;
     float col_in[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
-        col_in[i] = (u0 + i >= 1 && u0 + i < p.w - 1) ? 1.0f : 0.0f;
-    int cur = 0;
+        col_in[i] = (u0 + i >= 1 && u0 + i < w - 1) ? 1.0f : 0.0f;
+    int cur  = 0;
+    int roff = (v0 + 1) * w;  // row offset of row v + 1
 #pragma unroll 1
     for (int v = v0; v < v1; ++v) {
         uint4* const sc = cur ? stg1 : stg0;  // row v+1 and the tables of row v
         uint4* const sn = cur ? stg0 : stg1;
         cur ^= 1;
         cp_async_wait_all();
-        commit<FEAT, IN>(fetch_raw<R>(p, use_f, sc, T), dn);
+        commit<FEAT, IN>(fetch_raw<R>(L, ufac, sc, T), dn);
         const rtabs<FEAT> tb = fetch_tabs<FEAT>(p, sc + kRawSlots * T, T);
-        issue_raw<R>(p, A, Bf, v + 2, u0, use_f, sn, T);
-        issue_tabs<FEAT>(p, v + 1, u0, sn + kRawSlots * T, T);
-        cp_async_commit();
+        {
+            const bool in2 = v + 2 < h;
+            issue_raw<R>(L, in2 ? roff + w : roff - w, in2, sn, T);
+            issue_tabs<FEAT>(p, v + 1, roff + u0, u0, sn + kRawSlots * T, T);
+            cp_async_commit();
+        }
         at.v               = v;
-        at.oa              = size_t(fa) * p.frame_px + size_t(v) * p.w + u0;
-        at.ob              = size_t(fb) * p.frame_px + size_t(v) * p.w + u0;
-        const float row_in = (v >= 1 && v < p.h - 1) ? 1.0f : 0.0f;
+        const float row_in = (v >= 1 && v < h - 1) ? 1.0f : 0.0f;
 #pragma unroll
         for (int i = 0; i < 4; ++i)
             at.inside[i] = col_in[i] * row_in;
@@ -409,6 +435,9 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT>())
             curvature_row<OUT>(p, up, mid, dn, tb, at, cc);
         up  = mid;
         mid = dn;
+        roff += w;
+        at.oa += w;
+        at.ob += w;
     }
     cp_async_wait_all();
 }
