@@ -238,6 +238,8 @@ int validate_job(dc_ctx* c, const dc_job* j) {
 }
 
 // ---------------------------------------------------------------------------
+bool aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
+
 // Rows a thread of the frame-pair kernels marches over (tuning knob:
 // DC_ROWS_PER_STRIP in the environment, read once).
 int rows_per_strip() {
@@ -270,11 +272,54 @@ cudaError_t launch_pair(const dc::kparams& p, int n_frames, cudaStream_t s) {
     return cudaGetLastError();
 }
 
+template <int IN, int OUT>
+cudaError_t launch_flexion_pair(const dc::kparams& p, int n_frames, cudaStream_t s) {
+    const int       rps     = 2 * rows_per_strip();  // a longer march amortises the point window
+    const long long strips  = (p.h + rps - 1) / rps;
+    const long long pairs   = (n_frames + 1) / 2;
+    const long long threads = pairs * strips * (p.w / 2);
+    const long long blocks  = (threads + dc::pr::kPairThreads - 1) / dc::pr::kPairThreads;
+    if (blocks > 0x7fffffffLL)
+        return cudaErrorInvalidConfiguration;
+    static const cudaError_t carve = cudaFuncSetAttribute(
+        dc::pr::flexion_pair_kernel<IN, OUT>, cudaFuncAttributePreferredSharedMemoryCarveout,
+        int(cudaSharedmemCarveoutMaxShared));
+    if (carve != cudaSuccess)
+        return carve;
+    const size_t smem = size_t(2) * dc::pr::kFlexSlots * dc::pr::kPairThreads * sizeof(uint4);
+    dc::pr::flexion_pair_kernel<IN, OUT>
+        <<<unsigned(blocks), dc::pr::kPairThreads, smem, s>>>(p, n_frames, rps);
+    return cudaGetLastError();
+}
+
+// DC_RANGE / DC_SCALE with u16 input: the streaming kernel (8 pixels per thread,
+// frames walked inside the thread). Needs frames that are multiples of 8 pixels
+// and 16-byte aligned buffers.
+template <int FEAT, int IN, int OUT>
+cudaError_t launch_stream(const dc::kparams& p, int n_frames, cudaStream_t s) {
+    const int groups = int(p.frame_px / 8);
+    const int bx     = (groups + 255) / 256;
+    // about 8 resident blocks per SM; at least 4 frames per thread when possible
+    int by = std::max(1, std::min((148 * 8 + bx - 1) / bx, (n_frames + 3) / 4));
+    by     = std::min(by, 65535);
+    dc::pr::stream_kernel<FEAT, IN, OUT><<<dim3(bx, by, 1), 256, 0, s>>>(p, n_frames, groups);
+    return cudaGetLastError();
+}
+
 template <int FEAT, int IN, int OUT>
 cudaError_t launch_px(const dc::kparams& p, int n_frames, cudaStream_t s, bool vec4, bool fast) {
+    if constexpr (IN != dc::IN_F32_RANGE && (FEAT == dc::FEAT_RANGE || FEAT == dc::FEAT_SCALE)) {
+        bool ok = vec4 && (p.frame_px % 8) == 0 && aligned(p.in, 16) && aligned(p.out[0], 16);
+        if (ok)
+            return launch_stream<FEAT, IN, OUT>(p, n_frames, s);
+    }
     if constexpr (IN != dc::IN_F32_RANGE && has_pair_kernel<FEAT>()) {
         if (vec4 && fast)
             return launch_pair<FEAT, IN, OUT>(p, n_frames, s);
+    }
+    if constexpr (IN != dc::IN_F32_RANGE && FEAT == dc::FEAT_FLEXION) {
+        if (vec4 && fast)
+            return launch_flexion_pair<IN, OUT>(p, n_frames, s);
     }
     const int px = vec4 ? 4 : 1;
     const int qw = (p.w + px - 1) / px;
@@ -331,7 +376,6 @@ cudaError_t launch_in(const dc::kparams& p, int in_kind, int out_kind, int n, cu
     }
 }
 
-bool aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
 
 // Enqueue the fused kernel(s) for `job` (device pointers) on stream `s`.
 int launch_job(dc_ctx* c, const dc_job* j, cudaStream_t s) {

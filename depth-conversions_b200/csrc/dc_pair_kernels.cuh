@@ -339,7 +339,7 @@ constexpr int min_blocks() {
 #ifdef DC_MIN_BLOCKS
     return DC_MIN_BLOCKS;
 #else
-    return 4;
+    return FEAT == FEAT_CURVATURE ? 3 : 4;  // curvature wants 168 registers (no spills)
 #endif
 }
 
@@ -440,6 +440,287 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT>())
         at.ob += w;
     }
     cp_async_wait_all();
+}
+
+// ===========================================================================
+// Flexion: conversion/depth_to_flexion.h:79-167. Same frame-pair marching, but a
+// thread owns 2 columns: the window holds the camera-frame points P = d * ray
+// (3 rows x 4 columns x 3 components x 2 frames = 72 registers), computed once
+// per position. Rows rotate by renaming (the step is instantiated three times).
+struct v3 {
+    f2 x, y, z;
+};
+__device__ __forceinline__ v3 sub3(const v3& a, const v3& b) {
+    return {sub2(a.x, b.x), sub2(a.y, b.y), sub2(a.z, b.z)};
+}
+// Eigen 3.3.7 Core/Redux.h:91-105: c0 + (c1 + c2)
+__device__ __forceinline__ f2 dot3(const v3& a, const v3& b) {
+    return add2(mul2(a.x, b.x), add2(mul2(a.y, b.y), mul2(a.z, b.z)));
+}
+// Eigen 3.3.7 Core/Dot.h:124-134 normalized(): n / sqrt(squaredNorm), the null
+// vector unchanged. Guard-free as in dc_math.cuh normalized3<true>: z clamped to
+// 2^-100 makes the three quotients of the null vector 0 = the input.
+__device__ __forceinline__ v3 normalized3(const v3& n) {
+    f2 z = dot3(n, n);
+    z    = make_float2(fmaxf(z.x, 7.888609052210118e-31f), fmaxf(z.y, 7.888609052210118e-31f));
+    f2       y;
+    const f2 s = sqrt2(z, y);
+    y          = rcp_refine2(s, y);
+    return {div2(n.x, s, y), div2(n.y, s, y), div2(n.z, s, y)};
+}
+// Eigen 3.3.7 Geometry/OrthoMethods.h:34-46
+__device__ __forceinline__ v3 cross3(const v3& a, const v3& b) {
+    return {sub2(mul2(a.y, b.z), mul2(a.z, b.y)), sub2(mul2(a.z, b.x), mul2(a.x, b.z)),
+            sub2(mul2(a.x, b.y), mul2(a.y, b.x))};
+}
+
+constexpr int kFlexSlots = 6;
+// slot 0: [A: 2 px | B: 2 px | A word with u0-1 (high half) | B word with u0-1]
+// slot 1: [A word with u0+2 (low half) | B word | factor(u0-1) | factor(u0+2)]
+// slot 2: [factor(u0), factor(u0+1) | ray_x(u0-1) | ray_x(u0+2)]
+// slot 3: [ray_x(u0), ray_x(u0+1) | ray_y(u0), ray_y(u0+1)]
+// slot 4: [ray_z(u0), ray_z(u0+1) | ray_y(u0-1) | ray_y(u0+2)]
+// slot 5: [ray_z(u0-1) | ray_z(u0+2) | - | -]
+struct flane {
+    const unsigned short *A, *Bf;
+    const float *         fac, *rx, *ry, *rz;  // tables at column u0 (fac may be nullptr)
+    bool                  hl, hr;
+};
+
+__device__ __forceinline__ void flex_issue(const flane& L, int roff, bool in, uint4* st, int T) {
+    const bool l = in && L.hl, r = in && L.hr;
+    const int  ol = L.hl ? -2 : 0, orr = L.hr ? 2 : 0, ol1 = L.hl ? -1 : 0;
+    char *     s0 = reinterpret_cast<char*>(st), *s1 = reinterpret_cast<char*>(st + T),
+         *s2 = reinterpret_cast<char*>(st + 2 * T), *s3 = reinterpret_cast<char*>(st + 3 * T),
+         *s4 = reinterpret_cast<char*>(st + 4 * T), *s5 = reinterpret_cast<char*>(st + 5 * T);
+    const unsigned short *a = L.A + roff, *b = L.Bf + roff;
+    cp_async<4>(s0, a, in);
+    cp_async<4>(s0 + 4, b, in);
+    cp_async<4>(s0 + 8, a + ol, l);
+    cp_async<4>(s0 + 12, b + ol, l);
+    cp_async<4>(s1, a + orr, r);
+    cp_async<4>(s1 + 4, b + orr, r);
+    if (L.fac != nullptr) {
+        const float* f = L.fac + roff;
+        cp_async<4>(s1 + 8, f + ol1, l);
+        cp_async<4>(s1 + 12, f + orr, r);
+        cp_async<8>(s2, f, in);
+    }
+    const float *x = L.rx + roff, *y = L.ry + roff, *z = L.rz + roff;
+    cp_async<4>(s2 + 8, x + ol1, l);
+    cp_async<4>(s2 + 12, x + orr, r);
+    cp_async<8>(s3, x, in);
+    cp_async<8>(s3 + 8, y, in);
+    cp_async<8>(s4, z, in);
+    cp_async<4>(s4 + 8, y + ol1, l);
+    cp_async<4>(s4 + 12, y + orr, r);
+    cp_async<4>(s5, z + ol1, l);
+    cp_async<4>(s5 + 4, z + orr, r);
+}
+
+// to_camera (:70-76): P = d * ray for columns u0-1 .. u0+2 of both frames
+template <int IN>
+__device__ __forceinline__ void flex_points(const flane& L, float ufac, const uint4* st, int T,
+                                            v3 (&P)[4]) {
+    const uint4  q0 = st[0], q1 = st[T];
+    const float4 q2 = *reinterpret_cast<const float4*>(st + 2 * T);
+    const float4 q3 = *reinterpret_cast<const float4*>(st + 3 * T);
+    const float4 q4 = *reinterpret_cast<const float4*>(st + 4 * T);
+    const float4 q5 = *reinterpret_cast<const float4*>(st + 5 * T);
+    f2           d[4];
+    d[0] = make_float2(magic_hi(q0.z), magic_hi(q0.w));
+    d[1] = make_float2(magic_lo(q0.x), magic_lo(q0.y));
+    d[2] = make_float2(magic_hi(q0.x), magic_hi(q0.y));
+    d[3] = make_float2(magic_lo(q1.x), magic_lo(q1.y));
+    const bool  tab   = L.fac != nullptr;
+    const float fc[4] = {tab ? __uint_as_float(q1.z) : ufac, tab ? q2.x : ufac, tab ? q2.y : ufac,
+                         tab ? __uint_as_float(q1.w) : ufac};
+    const float rx[4] = {q2.z, q3.x, q3.y, q2.w};
+    const float ry[4] = {q4.z, q3.z, q3.w, q4.w};
+    const float rz[4] = {q5.x, q4.x, q4.y, q5.y};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        f2 r = add2(d[i], B(-8388608.0f));
+        if constexpr (IN == IN_U16_DEPTH)
+            r = mul2(r, B(fc[i]));
+        P[i] = {mul2(r, B(rx[i])), mul2(r, B(ry[i])), mul2(r, B(rz[i]))};
+    }
+}
+
+#ifndef DC_FLEX_BLOCKS
+#define DC_FLEX_BLOCKS 3
+#endif
+template <int IN, int OUT>
+__global__ void __launch_bounds__(kPairThreads, DC_FLEX_BLOCKS)
+    flexion_pair_kernel(const __grid_constant__ kparams p, int n_frames, int rows_per_strip) {
+    const int       groups_x = p.w >> 1;
+    const int       strips   = (p.h + rows_per_strip - 1) / rows_per_strip;
+    const long long gid      = (long long)blockIdx.x * kPairThreads + threadIdx.x;
+    const int       gx       = int(gid % groups_x);
+    const long long t        = gid / groups_x;
+    const int       strip    = int(t % strips);
+    const long long fp       = t / strips;
+    if (2 * fp >= n_frames)
+        return;
+    const long long fa = 2 * fp, fb = min(fa + 1, (long long)n_frames - 1);
+    const int u0 = gx * 2, w = p.w, h = p.h;
+    const int v0 = strip * rows_per_strip, v1 = min(v0 + rows_per_strip, h);
+    flane     L;
+    L.A   = static_cast<const unsigned short*>(p.in) + size_t(fa) * p.frame_px + u0;
+    L.Bf  = static_cast<const unsigned short*>(p.in) + size_t(fb) * p.frame_px + u0;
+    L.fac = (IN == IN_U16_DEPTH && p.range_factor.p != nullptr) ? p.range_factor.p + u0 : nullptr;
+    L.rx  = p.ray_x + u0;
+    L.ry  = p.ray_y + u0;
+    L.rz  = p.ray_z + u0;
+    L.hl  = u0 > 0;
+    L.hr  = u0 + 2 < w;
+    const float ufac = IN == IN_U16_DEPTH ? p.range_factor.value : 1.0f;
+
+    extern __shared__ uint4 smem[];
+    constexpr int T    = kPairThreads;
+    uint4* const  stg0 = smem + threadIdx.x;
+    uint4* const  stg1 = smem + kFlexSlots * T + threadIdx.x;
+
+    v3 w0[4], w1[4], w2[4];
+    flex_issue(L, max(v0 - 1, 0) * w, v0 >= 1, stg0, T);
+    flex_issue(L, v0 * w, true, stg1, T);
+    cp_async_commit();
+    cp_async_wait_all();
+    flex_points<IN>(L, ufac, stg0, T, w0);
+    flex_points<IN>(L, ufac, stg1, T, w1);
+    flex_issue(L, min(v0 + 1, h - 1) * w, v0 + 1 < h, stg0, T);
+    cp_async_commit();
+
+    using TO         = typename out_elem<OUT>::type;
+    TO* const   out  = static_cast<TO*>(p.out[0]);
+    size_t      oa   = size_t(fa) * p.frame_px + size_t(v0) * w + u0;
+    size_t      ob   = size_t(fb) * p.frame_px + size_t(v0) * w + u0;
+    const bool  cin0 = u0 >= 1, cin1 = u0 + 1 < w - 1;
+    int         cur = 0, roff = (v0 + 1) * w, v = v0;
+#define DC_FLEX_STEP(UP, MID, DN)                                                              \
+    {                                                                                          \
+        uint4* const sc = cur ? stg1 : stg0;                                                   \
+        uint4* const sn = cur ? stg0 : stg1;                                                   \
+        cur ^= 1;                                                                              \
+        cp_async_wait_all();                                                                   \
+        flex_points<IN>(L, ufac, sc, T, DN);                                                   \
+        const bool in2 = v + 2 < h;                                                            \
+        flex_issue(L, in2 ? roff + w : roff - w, in2, sn, T);                                  \
+        cp_async_commit();                                                                     \
+        const bool rin = v >= 1 && v < h - 1;                                                  \
+        f2         f[2];                                                                       \
+        _Pragma("unroll") for (int i = 0; i < 2; ++i) {                                        \
+            const int c  = i + 1;                                                              \
+            /* :105-127: (u,v-1)->(u,v+1), (u-1,v)->(u+1,v), (u+1,v-1)->(u-1,v+1),        */   \
+            /*           (u-1,v-1)->(u+1,v+1)                                              */   \
+            const v3 n0 = normalized3(sub3(DN[c], UP[c]));                                     \
+            const v3 n1 = normalized3(sub3(MID[c + 1], MID[c - 1]));                           \
+            const v3 n2 = normalized3(sub3(DN[c - 1], UP[c + 1]));                             \
+            const v3 n3 = normalized3(sub3(DN[c + 1], UP[c - 1]));                             \
+            const f2 x  = dot3(cross3(n0, n1), cross3(n2, n3));                                \
+            const bool ok = rin && (i == 0 ? cin0 : cin1);                                     \
+            f[i] = make_float2(ok ? fminf(fabsf(x.x), 1.0f) : 0.0f,                            \
+                               ok ? fminf(fabsf(x.y), 1.0f) : 0.0f);                           \
+        }                                                                                      \
+        if constexpr (OUT == OUT_U16) {                                                        \
+            const f2 s0 = add2(mul2(f[0], B(65535.0f)), B(12582912.0f));                       \
+            const f2 s1 = add2(mul2(f[1], B(65535.0f)), B(12582912.0f));                       \
+            *reinterpret_cast<unsigned*>(out + oa) =                                           \
+                __byte_perm(__float_as_uint(s0.x), __float_as_uint(s1.x), 0x5410);             \
+            *reinterpret_cast<unsigned*>(out + ob) =                                           \
+                __byte_perm(__float_as_uint(s0.y), __float_as_uint(s1.y), 0x5410);             \
+        } else {                                                                               \
+            *reinterpret_cast<float2*>(out + oa) = make_float2(f[0].x, f[1].x);                \
+            *reinterpret_cast<float2*>(out + ob) = make_float2(f[0].y, f[1].y);                \
+        }                                                                                      \
+        roff += w;                                                                             \
+        oa += w;                                                                               \
+        ob += w;                                                                               \
+        if (++v >= v1)                                                                         \
+            break;                                                                             \
+    }
+    for (;;) {
+        DC_FLEX_STEP(w0, w1, w2)
+        DC_FLEX_STEP(w1, w2, w0)
+        DC_FLEX_STEP(w2, w0, w1)
+    }
+#undef DC_FLEX_STEP
+    cp_async_wait_all();
+}
+
+// ===========================================================================
+// Streaming kernel for the two HBM-bound jobs: DC_RANGE (depth_to_laserscan.h:
+// 54-93 + the u16 conversion of converter_laserscan.h.inl:9-10) and DC_SCALE
+// (depth_scaling.h:21-31). A thread owns 8 consecutive pixels of the frame
+// (one 16-byte load), keeps their range factors in registers and walks over the
+// frames of the batch, four frames in flight, so the factor table is read once
+// per thread instead of once per frame.
+template <int FEAT, int IN, int OUT>
+__global__ void __launch_bounds__(256)
+    stream_kernel(const __grid_constant__ kparams p, int n_frames, int groups_per_frame) {
+    const int g = blockIdx.x * 256 + threadIdx.x;
+    if (g >= groups_per_frame)
+        return;
+    f2 fac[4];
+    if constexpr (FEAT == FEAT_RANGE && IN == IN_U16_DEPTH) {
+        if (p.range_factor.p != nullptr) {
+            const float4 a = __ldg(reinterpret_cast<const float4*>(p.range_factor.p) + 2 * g);
+            const float4 b = __ldg(reinterpret_cast<const float4*>(p.range_factor.p) + 2 * g + 1);
+            fac[0] = make_float2(a.x, a.y), fac[1] = make_float2(a.z, a.w);
+            fac[2] = make_float2(b.x, b.y), fac[3] = make_float2(b.z, b.w);
+        } else {
+            fac[0] = fac[1] = fac[2] = fac[3] = B(p.range_factor.value);
+        }
+    }
+    const uint4* in = static_cast<const uint4*>(p.in) + g;
+    const size_t fstride = size_t(groups_per_frame);  // uint4 per frame
+    constexpr int K = 4;
+    for (int f0 = blockIdx.y; f0 < n_frames; f0 += K * gridDim.y) {
+        uint4 raw[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const int f = f0 + k * gridDim.y;
+            if (f < n_frames)
+                raw[k] = __ldcs(in + size_t(f) * fstride);
+        }
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const int f = f0 + k * gridDim.y;
+            if (f >= n_frames)
+                break;
+            const unsigned wd[4] = {raw[k].x, raw[k].y, raw[k].z, raw[k].w};
+            f2             v[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                v[i] = add2(make_float2(magic_lo(wd[i]), magic_hi(wd[i])), B(-8388608.0f));
+                if constexpr (FEAT == FEAT_RANGE && IN == IN_U16_DEPTH)
+                    v[i] = mul2(v[i], fac[i]);
+                if constexpr (FEAT == FEAT_SCALE)
+                    v[i] = add2(mul2(v[i], B(p.s_scale)), B(p.s_offset));
+            }
+            const size_t o = size_t(f) * fstride + g;
+            if constexpr (OUT == OUT_U16) {
+                unsigned q[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    if constexpr (FEAT == FEAT_SCALE) {
+                        // any sign / magnitude: cvRound + saturate_cast<ushort>
+                        q[i] = unsigned(sat_u16_rn(v[i].x)) | (unsigned(sat_u16_rn(v[i].y)) << 16);
+                    } else {
+                        // 0 <= range: clamp above, round half to even by the magic add
+                        const f2 c = make_float2(fminf(v[i].x, 65535.0f), fminf(v[i].y, 65535.0f));
+                        const f2 m = add2(c, B(12582912.0f));
+                        q[i] = __byte_perm(__float_as_uint(m.x), __float_as_uint(m.y), 0x5410);
+                    }
+                }
+                __stcs(static_cast<uint4*>(p.out[0]) + o, make_uint4(q[0], q[1], q[2], q[3]));
+            } else {
+                float4* dst = static_cast<float4*>(p.out[0]) + 2 * o;
+                __stcs(dst, make_float4(v[0].x, v[0].y, v[1].x, v[1].y));
+                __stcs(dst + 1, make_float4(v[2].x, v[2].y, v[3].x, v[3].y));
+            }
+        }
+    }
 }
 
 }  // namespace pr
