@@ -30,7 +30,9 @@ EXPORTED_SYMBOLS = [
     "dc_set_pinhole", "dc_set_equirectangular", "dc_set_frame_size", "dc_width",
     "dc_height", "dc_convert_device", "dc_convert_host", "dc_synchronize",
     "dc_host_alloc", "dc_host_free", "dc_synth_depth_device", "dc_kernel_launches",
+    "dc_quantise_host",
 ]
+DC_Q_RANGE, DC_Q_BEARING, DC_Q_FLEXION, DC_Q_CURVATURE, DC_Q_MAX_CURVE = range(5)
 
 
 class DcJob(C.Structure):
@@ -80,6 +82,8 @@ def lib():
         L.dc_host_free.restype = None
         L.dc_synth_depth_device.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int,
                                             C.c_void_p, C.c_void_p]
+        L.dc_quantise_host.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t,
+                                       C.c_void_p, C.c_float, C.c_float]
         L.dc_kernel_launches.restype = C.c_uint64
         L.dc_kernel_launches.argtypes = [C.c_void_p]
         _lib = L
@@ -184,6 +188,16 @@ class Context:
                             clamp, scale, offset)
         self._check(self.convert_host_raw(job))
         return [(o[0] if single else o) if o is not None else None for o in outs]
+
+    def quantise(self, quant, feature, mask=None, clamp=(-20.0, 20.0)):
+        """Stand-alone quantiser of the library API: float image -> u16 image."""
+        feature = np.ascontiguousarray(feature, np.float32)
+        out = np.empty(feature.shape, np.uint16)
+        m = np.ascontiguousarray(mask, np.float32) if mask is not None else None
+        self._check(self._L.dc_quantise_host(self._h, quant, feature.ctypes.data,
+                                             m.ctypes.data if m is not None else None,
+                                             feature.size, out.ctypes.data, clamp[0], clamp[1]))
+        return out
 
     def synth_depth_device(self, seed, frame0, n_frames, out_ptr, stream=None):
         self._check(self._L.dc_synth_depth_device(self._h, seed, frame0, n_frames,

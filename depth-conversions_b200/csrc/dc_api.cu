@@ -712,6 +712,53 @@ int dc_convert_host(dc_ctx* c, const dc_job* j) {
     return DC_OK;
 }
 
+int dc_quantise_host(dc_ctx* c, int quant, const float* feature, const float* mask, size_t n_px,
+                     uint16_t* out, float clamp_lo, float clamp_hi) {
+    if (c == nullptr)
+        return DC_ERR_INVALID;
+    if (c->sticky)
+        return DC_ERR_CUDA;
+    if (quant < DC_Q_RANGE || quant > DC_Q_MAX_CURVE)
+        return fail(c, DC_ERR_INVALID, "unknown quantiser");
+    if (n_px == 0)
+        return DC_OK;
+    if (feature == nullptr || out == nullptr)
+        return fail(c, DC_ERR_INVALID, "quantiser buffers are NULL");
+    if (quant == DC_Q_CURVATURE && (mask == nullptr || !(clamp_lo < clamp_hi)))
+        return fail(c, DC_ERR_INVALID,
+                    "curvature quantiser needs the range image as mask and lower < upper bound");
+    DC_CUDA(c, cudaSetDevice(c->device));
+    slot& s = c->slots[0];
+    int   rc = finish_slot(c, s);
+    if (rc != DC_OK)
+        return rc;
+    DC_CUDA(c, reserve_dev(s.d_in, n_px * sizeof(float)));
+    DC_CUDA(c, reserve_dev(s.d_out[0], n_px * sizeof(float)));
+    DC_CUDA(c, reserve_dev(s.d_out[1], n_px * sizeof(uint16_t)));
+    DC_CUDA(c, cudaMemcpyAsync(s.d_in.p, feature, n_px * sizeof(float), cudaMemcpyHostToDevice,
+                               s.stream));
+    if (quant == DC_Q_CURVATURE)
+        DC_CUDA(c, cudaMemcpyAsync(s.d_out[0].p, mask, n_px * sizeof(float),
+                                   cudaMemcpyHostToDevice, s.stream));
+    // conversion/util.h:71-79 scaling_factor<float, ushort>(max_angle)
+    const float pi_f  = float(3.141592653589793238462);
+    const float alpha = quant == DC_Q_BEARING     ? 65535.0f / pi_f
+                        : quant == DC_Q_MAX_CURVE ? 65535.0f / float(2. * double(pi_f))
+                                                  : 65535.0f;
+    const unsigned blocks = unsigned(std::min<size_t>((n_px + 255) / 256, 148 * 16));
+    dc::quantise_kernel<<<blocks, 256, 0, s.stream>>>(
+        quant, static_cast<const float*>(s.d_in.p), static_cast<const float*>(s.d_out[0].p), n_px,
+        static_cast<unsigned short*>(s.d_out[1].p), alpha, clamp_lo, clamp_hi);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess)
+        return cuda_fail(c, e, "quantise kernel launch");
+    c->launches += 1;
+    DC_CUDA(c, cudaMemcpyAsync(out, s.d_out[1].p, n_px * sizeof(uint16_t), cudaMemcpyDeviceToHost,
+                               s.stream));
+    DC_CUDA(c, cudaStreamSynchronize(s.stream));
+    return DC_OK;
+}
+
 int dc_synchronize(dc_ctx* c) {
     if (c == nullptr)
         return DC_ERR_INVALID;

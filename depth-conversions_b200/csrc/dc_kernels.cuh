@@ -458,6 +458,20 @@ __global__ void __launch_bounds__(256)
     }
 }
 
+// Stand-alone quantisers (dc_quantise_host): float feature image -> u16.
+enum : int { Q_RANGE = 0, Q_BEARING = 1, Q_FLEXION = 2, Q_CURVATURE = 3, Q_MAX_CURVE = 4 };
+__global__ void __launch_bounds__(256)
+    quantise_kernel(int quant, const float* __restrict__ in, const float* __restrict__ mask,
+                    size_t n, unsigned short* __restrict__ out, float alpha, float lo, float hi) {
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+         i += size_t(gridDim.x) * blockDim.x) {
+        const float v = in[i];
+        out[i] = quant == Q_CURVATURE ? quant_curvature(v, mask[i], lo, hi)
+                 : quant == Q_RANGE   ? sat_u16_rn(v)
+                                      : quant_scale(v, alpha);
+    }
+}
+
 // Synthetic depth generator (bench / test tooling), bit-identical to
 // oracle/dc_oracle.c dco_synth_depth.
 __device__ __forceinline__ unsigned long long splitmix64(unsigned long long x) {

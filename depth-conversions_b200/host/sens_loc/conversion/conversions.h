@@ -1,0 +1,188 @@
+// sens_loc::conversion::* -- the drop-in replacements of the reference's
+// depth -> feature functions for Real = float, same names and argument meaning
+// (src/include/sens_loc/conversion/*.h). Every function checks its sizes, hands
+// the pixels to libdepthconv_b200.so (sm_100a kernels) and returns an owning
+// image; nothing is computed on the host.
+//
+// Differences to the reference, all at the edges:
+//   * precondition violations (image size != intrinsic size, empty image) throw
+//     std::invalid_argument; the reference's GSL contracts terminate;
+//   * a GPU failure throws sens_loc::gpu::error (the reference cannot fail);
+//   * the par_* variants take no tf::Taskflow: the GPU batches frames instead
+//     of rows. depth_to_*_batch() is the many-frames form the tool uses.
+#ifndef DCB200_SENS_LOC_CONVERSION_H
+#define DCB200_SENS_LOC_CONVERSION_H
+
+#include "../gpu/context.h"
+#include "../math/image.h"
+
+#include <optional>
+#include <stdexcept>
+
+namespace sens_loc::conversion {
+
+/// conversion/util.h:18-27
+enum class direction { horizontal, vertical, diagonal, antidiagonal };
+
+namespace detail {
+template <typename Intrinsic, typename T>
+inline void expect_same_size(const math::image<T>& img, const Intrinsic& k) {
+    if (img.empty() || img.w() != k.w() || img.h() != k.h())
+        throw std::invalid_argument("conversion: image size does not match the intrinsic");
+}
+inline dc_job job(int feature, int in_kind, int out_kind, const void* in) {
+    dc_job j{};
+    j.feature = feature, j.in_kind = in_kind, j.out_kind = out_kind, j.n_frames = 1;
+    j.in       = in;
+    j.clamp_lo = -20.f, j.clamp_hi = 20.f;
+    j.scale = 1., j.offset = 0.;
+    return j;
+}
+template <typename Intrinsic>
+inline math::image<float> one_output(int feature, int slot, const math::image<float>& range,
+                                     const Intrinsic& k) {
+    expect_same_size(range, k);
+    gpu::context& g = gpu::context::mine();
+    g.use(k);
+    math::image<float> out(range.w(), range.h());
+    dc_job             j = job(feature, DC_IN_F32_RANGE, DC_OUT_F32, range.data());
+    j.out[slot]          = out.data();
+    g.convert_host(j);
+    return out;
+}
+}  // namespace detail
+
+/// depth_to_laserscan.h:70-93: orthographic depth -> Euclidean range.
+template <typename Real = float, typename PixelType = ushort, typename Intrinsic>
+inline math::image<Real> depth_to_laserscan(const math::image<PixelType>& depth_image,
+                                            const Intrinsic&              intrinsic) {
+    static_assert(std::is_same_v<Real, float> && std::is_same_v<PixelType, ushort>,
+                  "the B200 path carries Real = float, PixelType = ushort");
+    detail::expect_same_size(depth_image, intrinsic);
+    gpu::context& g = gpu::context::mine();
+    g.use(intrinsic);
+    math::image<float> out(depth_image.w(), depth_image.h());
+    dc_job j = detail::job(DC_RANGE, DC_IN_U16_DEPTH, DC_OUT_F32, depth_image.data());
+    j.out[0] = out.data();
+    g.convert_host(j);
+    return out;
+}
+
+/// depth_to_bearing.h:221-248
+template <direction Direction, typename Real = float, typename Intrinsic>
+inline math::image<Real> depth_to_bearing(const math::image<Real>& depth_image,
+                                          const Intrinsic&         intrinsic) {
+    static_assert(std::is_same_v<Real, float>);
+    return detail::one_output(DC_BEARING, int(Direction), depth_image, intrinsic);
+}
+/// All requested directions in one pass over the image (the reference makes one
+/// pass per direction, converter_bearing.h.inl:13-26). Slots not wanted stay empty.
+template <typename Intrinsic>
+inline void depth_to_bearing_all(const math::image<float>& depth_image, const Intrinsic& intrinsic,
+                                 const bool (&want)[4], math::image<float> (&out)[4]) {
+    detail::expect_same_size(depth_image, intrinsic);
+    gpu::context& g = gpu::context::mine();
+    g.use(intrinsic);
+    dc_job j = detail::job(DC_BEARING, DC_IN_F32_RANGE, DC_OUT_F32, depth_image.data());
+    for (int d = 0; d < 4; ++d)
+        if (want[d]) {
+            out[d]   = math::image<float>(depth_image.w(), depth_image.h());
+            j.out[d] = out[d].data();
+        }
+    g.convert_host(j);
+}
+
+/// depth_to_flexion.h:147-167
+template <typename Intrinsic>
+inline math::image<float> depth_to_flexion(const math::image<float>& depth_image,
+                                           const Intrinsic&          intrinsic) {
+    return detail::one_output(DC_FLEXION, 0, depth_image, intrinsic);
+}
+/// depth_to_curvature.h:166-184
+template <typename Intrinsic>
+inline math::image<float> depth_to_gaussian_curvature(const math::image<float>& depth_image,
+                                                      const Intrinsic&          intrinsic) {
+    return detail::one_output(DC_CURVATURE, 0, depth_image, intrinsic);
+}
+/// depth_to_curvature.h:188-206
+template <typename Intrinsic>
+inline math::image<float> depth_to_mean_curvature(const math::image<float>& depth_image,
+                                                  const Intrinsic&          intrinsic) {
+    return detail::one_output(DC_CURVATURE, 1, depth_image, intrinsic);
+}
+/// depth_to_max_curve.h:86-153
+template <typename Intrinsic>
+inline math::image<float> depth_to_max_curve(const math::image<float>& depth_image,
+                                             const Intrinsic&          intrinsic) {
+    return detail::one_output(DC_MAX_CURVE, 0, depth_image, intrinsic);
+}
+
+// ---- quantisers -----------------------------------------------------------
+namespace detail {
+inline math::image<ushort> quantise(int quant, const math::image<float>& img,
+                                    const math::image<float>* mask, float lo, float hi) {
+    if (img.empty() || (mask != nullptr && (mask->w() != img.w() || mask->h() != img.h())))
+        throw std::invalid_argument("quantiser: empty image or mask of another size");
+    math::image<ushort> out(img.w(), img.h());
+    gpu::context::mine().quantise(quant, img.data(), mask != nullptr ? mask->data() : nullptr,
+                                  img.pixels(), out.data(), lo, hi);
+    return out;
+}
+}  // namespace detail
+
+/// depth_to_bearing.h:282-301
+template <typename Real = float, typename PixelType = ushort>
+inline math::image<PixelType> convert_bearing(const math::image<Real>& bearing_image) {
+    static_assert(std::is_same_v<Real, float> && std::is_same_v<PixelType, ushort>);
+    return detail::quantise(DC_Q_BEARING, bearing_image, nullptr, 0.f, 0.f);
+}
+/// depth_to_flexion.h:194-215
+template <typename PixelType = ushort, typename Real = float>
+inline math::image<PixelType> convert_flexion(const math::image<Real>& flexion_image) {
+    static_assert(std::is_same_v<Real, float> && std::is_same_v<PixelType, ushort>);
+    return detail::quantise(DC_Q_FLEXION, flexion_image, nullptr, 0.f, 0.f);
+}
+/// depth_to_max_curve.h:156-176
+template <typename PixelType = ushort, typename Real = float>
+inline math::image<PixelType> convert_max_curve(const math::image<Real>& max_curve_image) {
+    static_assert(std::is_same_v<Real, float> && std::is_same_v<PixelType, ushort>);
+    return detail::quantise(DC_Q_MAX_CURVE, max_curve_image, nullptr, 0.f, 0.f);
+}
+/// depth_to_curvature.h:253-283. Both clamps are required here (the tool always
+/// passes them, converter_curvature.h.inl:9-10); the min/max-of-image form is
+/// not provided and throws.
+template <typename PixelType = ushort, typename Real = float, typename MaskType = float>
+inline math::image<PixelType> curvature_to_image(const math::image<Real>&     curvature_img,
+                                                 const math::image<MaskType>& depth_image_as_mask,
+                                                 std::optional<Real> clamp_min = std::nullopt,
+                                                 std::optional<Real> clamp_max = std::nullopt) {
+    static_assert(std::is_same_v<Real, float> && std::is_same_v<PixelType, ushort> &&
+                  std::is_same_v<MaskType, float>);
+    if (!clamp_min || !clamp_max)
+        throw std::invalid_argument("curvature_to_image: both clamps are required on the B200 path");
+    return detail::quantise(DC_Q_CURVATURE, curvature_img, &depth_image_as_mask, *clamp_min,
+                            *clamp_max);
+}
+/// range image -> 16 bit, apps/depth2x/converter_laserscan.h.inl:9-10
+inline math::image<ushort> convert_range(const math::image<float>& range_image) {
+    return detail::quantise(DC_Q_RANGE, range_image, nullptr, 0.f, 0.f);
+}
+
+/// depth_scaling.h:21-31: saturate(round(depth * scale + offset))
+inline math::image<ushort> depth_scaling(const math::image<ushort>& depth_image, double scale,
+                                         double offset) {
+    if (depth_image.empty())
+        throw std::invalid_argument("depth_scaling: empty image");
+    gpu::context& g = gpu::context::mine();
+    g.use_frame_size(depth_image.w(), depth_image.h());
+    math::image<ushort> out(depth_image.w(), depth_image.h());
+    dc_job j = detail::job(DC_SCALE, DC_IN_U16_RANGE, DC_OUT_U16, depth_image.data());
+    j.out[0] = out.data();
+    j.scale  = scale;
+    j.offset = offset;
+    g.convert_host(j);
+    return out;
+}
+
+}  // namespace sens_loc::conversion
+#endif

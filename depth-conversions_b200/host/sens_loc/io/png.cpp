@@ -1,0 +1,221 @@
+#include "png.h"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <zlib.h>
+
+namespace sens_loc::io::png {
+namespace {
+
+const unsigned char kSig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+
+std::uint32_t be32(const unsigned char* p) {
+    return (std::uint32_t(p[0]) << 24) | (std::uint32_t(p[1]) << 16) | (std::uint32_t(p[2]) << 8) |
+           std::uint32_t(p[3]);
+}
+void put32(std::vector<unsigned char>& v, std::uint32_t x) {
+    v.push_back((unsigned char)(x >> 24));
+    v.push_back((unsigned char)(x >> 16));
+    v.push_back((unsigned char)(x >> 8));
+    v.push_back((unsigned char)x);
+}
+void chunk(std::vector<unsigned char>& out, const char type[4], const unsigned char* data,
+           std::size_t n) {
+    put32(out, std::uint32_t(n));
+    const std::size_t at = out.size();
+    out.insert(out.end(), type, type + 4);
+    if (n != 0)
+        out.insert(out.end(), data, data + n);
+    put32(out, std::uint32_t(crc32(0L, out.data() + at, uInt(n + 4))));
+}
+int paeth(int a, int b, int c) {
+    const int p = a + b - c, pa = std::abs(p - a), pb = std::abs(p - b), pc = std::abs(p - c);
+    return (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
+}
+
+}  // namespace
+
+status read_file(const std::string& path, std::vector<unsigned char>& bytes, info& hdr) {
+    std::FILE* f = std::fopen(path.c_str(), "rb");
+    if (f == nullptr)
+        return status::io_error;
+    std::fseek(f, 0, SEEK_END);
+    const long n = std::ftell(f);
+    std::fseek(f, 0, SEEK_SET);
+    if (n < 0) {
+        std::fclose(f);
+        return status::io_error;
+    }
+    bytes.resize(std::size_t(n));
+    const std::size_t got = n != 0 ? std::fread(bytes.data(), 1, std::size_t(n), f) : 0;
+    std::fclose(f);
+    if (got != std::size_t(n))
+        return status::io_error;
+    if (n < 8 + 25 || std::memcmp(bytes.data(), kSig, 8) != 0)
+        return status::not_png;
+    const unsigned char* p = bytes.data() + 8;
+    if (be32(p) != 13 || std::memcmp(p + 4, "IHDR", 4) != 0)
+        return status::corrupt;
+    hdr.w          = int(be32(p + 8));
+    hdr.h          = int(be32(p + 12));
+    hdr.bit_depth  = p[16];
+    hdr.color_type = p[17];
+    hdr.interlace  = p[20];
+    if (hdr.w <= 0 || hdr.h <= 0 || p[18] != 0 || p[19] != 0)
+        return status::corrupt;
+    return status::ok;
+}
+
+status decode_grey(const std::vector<unsigned char>& bytes, const info& hdr, void* dst,
+                   std::vector<unsigned char>& scratch) {
+    if (hdr.color_type != 0 || hdr.interlace != 0 || (hdr.bit_depth != 8 && hdr.bit_depth != 16))
+        return status::unsupported;
+    const std::size_t bpp = std::size_t(hdr.bit_depth / 8), row = std::size_t(hdr.w) * bpp;
+    const std::size_t raw_size = (row + 1) * std::size_t(hdr.h);
+    scratch.resize(raw_size);
+
+    z_stream zs{};
+    if (inflateInit(&zs) != Z_OK)
+        return status::corrupt;
+    zs.next_out  = scratch.data();
+    zs.avail_out = uInt(raw_size);
+    int         zr  = Z_OK;
+    std::size_t pos = 8;
+    bool        end = false;
+    while (!end && pos + 12 <= bytes.size()) {
+        const std::uint32_t  len  = be32(bytes.data() + pos);
+        const unsigned char* type = bytes.data() + pos + 4;
+        if (pos + 12 + len > bytes.size())
+            break;
+        if (std::memcmp(type, "IDAT", 4) == 0 && zr == Z_OK) {
+            zs.next_in  = const_cast<unsigned char*>(type + 4);
+            zs.avail_in = len;
+            zr          = inflate(&zs, Z_NO_FLUSH);
+        } else if (std::memcmp(type, "IEND", 4) == 0) {
+            end = true;
+        }
+        pos += 12 + len;
+    }
+    const bool complete = zs.total_out == raw_size && (zr == Z_STREAM_END || zr == Z_OK);
+    inflateEnd(&zs);
+    if (!complete)
+        return status::corrupt;
+
+    unsigned char*       out  = static_cast<unsigned char*>(dst);
+    const unsigned char* prev = nullptr;
+    for (int y = 0; y < hdr.h; ++y) {
+        unsigned char* line = scratch.data() + std::size_t(y) * (row + 1);
+        const int      ft   = line[0];
+        unsigned char* cur  = line + 1;
+        switch (ft) {
+        case 0: break;
+        case 1:
+            for (std::size_t i = bpp; i < row; ++i)
+                cur[i] = (unsigned char)(cur[i] + cur[i - bpp]);
+            break;
+        case 2:
+            if (prev != nullptr)
+                for (std::size_t i = 0; i < row; ++i)
+                    cur[i] = (unsigned char)(cur[i] + prev[i]);
+            break;
+        case 3:
+            for (std::size_t i = 0; i < row; ++i) {
+                const int a = i >= bpp ? cur[i - bpp] : 0, b = prev != nullptr ? prev[i] : 0;
+                cur[i]      = (unsigned char)(cur[i] + ((a + b) >> 1));
+            }
+            break;
+        case 4:
+            for (std::size_t i = 0; i < row; ++i) {
+                const int a = i >= bpp ? cur[i - bpp] : 0, b = prev != nullptr ? prev[i] : 0;
+                const int c = (i >= bpp && prev != nullptr) ? prev[i - bpp] : 0;
+                cur[i]      = (unsigned char)(cur[i] + paeth(a, b, c));
+            }
+            break;
+        default: return status::corrupt;
+        }
+        unsigned char* o = out + std::size_t(y) * row;
+        if (bpp == 2) {
+            for (std::size_t i = 0; i < row; i += 2) {  // big endian -> native (little endian)
+                o[i]     = cur[i + 1];
+                o[i + 1] = cur[i];
+            }
+        } else {
+            std::memcpy(o, cur, row);
+        }
+        prev = cur;
+    }
+    return status::ok;
+}
+
+status encode_grey(const void* src, int w, int h, int bit_depth, std::vector<unsigned char>& out,
+                   std::vector<unsigned char>& scratch, int level) {
+    if (w <= 0 || h <= 0 || (bit_depth != 8 && bit_depth != 16))
+        return status::unsupported;
+    const std::size_t bpp = std::size_t(bit_depth / 8), row = std::size_t(w) * bpp;
+    const std::size_t raw_size = (row + 1) * std::size_t(h);
+    const uLong       bound    = compressBound(uLong(raw_size));
+    scratch.resize(raw_size + bound);
+    unsigned char*       raw = scratch.data();
+    unsigned char*       zed = scratch.data() + raw_size;
+    const unsigned char* in  = static_cast<const unsigned char*>(src);
+    for (int y = 0; y < h; ++y) {  // filter type 1 (sub) on big-endian samples
+        unsigned char*       line = raw + std::size_t(y) * (row + 1);
+        const unsigned char* s    = in + std::size_t(y) * row;
+        line[0]                   = 1;
+        unsigned char* cur        = line + 1;
+        if (bpp == 2) {
+            unsigned pl = 0, ph = 0;
+            for (std::size_t i = 0; i < row; i += 2) {
+                const unsigned hi = s[i + 1], lo = s[i];
+                cur[i]     = (unsigned char)(hi - ph);
+                cur[i + 1] = (unsigned char)(lo - pl);
+                ph = hi, pl = lo;
+            }
+        } else {
+            unsigned p = 0;
+            for (std::size_t i = 0; i < row; ++i) {
+                cur[i] = (unsigned char)(s[i] - p);
+                p      = s[i];
+            }
+        }
+    }
+    z_stream zs{};
+    if (deflateInit2(&zs, level, Z_DEFLATED, 15, 8, Z_RLE) != Z_OK)
+        return status::corrupt;
+    zs.next_in   = raw;
+    zs.avail_in  = uInt(raw_size);
+    zs.next_out  = zed;
+    zs.avail_out = uInt(bound);
+    const int zr = deflate(&zs, Z_FINISH);
+    const std::size_t zn = zs.total_out;
+    deflateEnd(&zs);
+    if (zr != Z_STREAM_END)
+        return status::corrupt;
+
+    out.clear();
+    out.reserve(zn + 64);
+    out.insert(out.end(), kSig, kSig + 8);
+    unsigned char ihdr[13];
+    const std::uint32_t uw = std::uint32_t(w), uh = std::uint32_t(h);
+    ihdr[0] = (unsigned char)(uw >> 24), ihdr[1] = (unsigned char)(uw >> 16);
+    ihdr[2] = (unsigned char)(uw >> 8), ihdr[3] = (unsigned char)uw;
+    ihdr[4] = (unsigned char)(uh >> 24), ihdr[5] = (unsigned char)(uh >> 16);
+    ihdr[6] = (unsigned char)(uh >> 8), ihdr[7] = (unsigned char)uh;
+    ihdr[8] = (unsigned char)bit_depth, ihdr[9] = 0, ihdr[10] = 0, ihdr[11] = 0, ihdr[12] = 0;
+    chunk(out, "IHDR", ihdr, 13);
+    chunk(out, "IDAT", zed, zn);
+    chunk(out, "IEND", nullptr, 0);
+    return status::ok;
+}
+
+status write_file(const std::string& path, const std::vector<unsigned char>& bytes) {
+    std::FILE* f = std::fopen(path.c_str(), "wb");
+    if (f == nullptr)
+        return status::io_error;
+    const std::size_t n = std::fwrite(bytes.data(), 1, bytes.size(), f);
+    const int         c = std::fclose(f);
+    return (n == bytes.size() && c == 0) ? status::ok : status::io_error;
+}
+
+}  // namespace sens_loc::io::png

@@ -171,6 +171,27 @@ int dc_convert_device(dc_ctx* ctx, const dc_job* job, void* cuda_stream);
  * frame pipeline make. */
 int dc_convert_host(dc_ctx* ctx, const dc_job* job);
 
+/* The stand-alone quantisers of the library API: float feature image -> the
+ * 16 bit image depth2x writes. (The depth2x path never calls this: DC_OUT_U16
+ * fuses the same arithmetic into the feature kernel.) */
+typedef enum dc_quant {
+    DC_Q_RANGE     = 0, /* cv::Mat::convertTo(CV_16U): apps/depth2x/converter_laserscan.h.inl:9-10 */
+    DC_Q_BEARING   = 1, /* convert_bearing<float, ushort>: conversion/depth_to_bearing.h:282-301 */
+    DC_Q_FLEXION   = 2, /* convert_flexion<ushort>: conversion/depth_to_flexion.h:194-215 */
+    DC_Q_CURVATURE = 3, /* curvature_to_image<ushort> with both clamps:
+                           conversion/depth_to_curvature.h:253-283; `mask` = the
+                           range image whose zeros blank the result */
+    DC_Q_MAX_CURVE = 4  /* convert_max_curve<ushort>: conversion/depth_to_max_curve.h:156-176 */
+} dc_quant;
+
+/* HOST buffers, synchronous. `mask` is read for DC_Q_CURVATURE only (n_px
+ * floats), clamp_lo < clamp_hi likewise. Needs no camera. The unclamped form of
+ * curvature_to_image (a global min/max reduction, depth_to_curvature.h:218-228)
+ * is never taken by depth2x (converter_curvature.h.inl:9-10) and is not
+ * provided: pass both clamps. */
+int dc_quantise_host(dc_ctx* ctx, int quant, const float* feature, const float* mask,
+                     size_t n_px, uint16_t* out, float clamp_lo, float clamp_hi);
+
 /* Block until all work this context enqueued on its own streams has finished. */
 int dc_synchronize(dc_ctx* ctx);
 
