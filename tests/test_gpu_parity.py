@@ -174,3 +174,72 @@ def test_bad_jobs_are_rejected(pkg, gpu_ctx):
     assert L.dc_set_pinhole(gpu_ctx._h, 32, 16, 1.0, -1.0, 1.0, 1.0) == P.DC_ERR_INVALID
     assert b"pinhole" in L.dc_last_error(gpu_ctx._h)
     assert gpu_ctx.size == (32, 16)
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 5])
+def test_batch_composition_does_not_change_results(pkg, gpu_ctx, oracle, n):
+    """The fast kernels convert two frames per thread (odd batches duplicate the
+    last frame): every frame of a batch must equal the same frame converted
+    alone, and the u16-input fast path must equal the one-frame kernels that
+    the float-input library API uses (bit for bit where the arithmetic is
+    IEEE-only)."""
+    w, h = 256, 75
+    k = kinect_scaled(w, h)
+    set_k(gpu_ctx, k)
+    frames = np.stack([oracle.synth_depth(0xD2C00009, f, w, h) for f in range(n)])
+    together = gpu_all_features(pkg, gpu_ctx, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)
+    together32 = gpu_all_features(pkg, gpu_ctx, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_F32)
+    rng = together32["range"]
+    for i in range(n):
+        alone = gpu_all_features(pkg, gpu_ctx, frames[i], pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)
+        alone32 = gpu_all_features(pkg, gpu_ctx, frames[i], pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_F32)
+        scalar32 = gpu_all_features(pkg, gpu_ctx, rng[i], pkg.DC_IN_F32_RANGE, pkg.DC_OUT_F32)
+        for name in together:
+            assert np.array_equal(together[name][i], alone[name]), name
+            assert np.array_equal(together32[name][i].view(np.uint32), alone32[name].view(np.uint32)), name
+        for name in ("range", "flexion", "gauss", "range_fused"):
+            assert np.array_equal(together32[name][i].view(np.uint32), scalar32[name].view(np.uint32)), name
+        for name in ("bearing_h", "bearing_v", "bearing_d", "bearing_a", "max_curve", "mean"):
+            assert_float_parity(name, together32[name][i], scalar32[name], exact=False)
+
+
+@pytest.mark.parametrize("w,h", [(1920, 1080), (4096, 2160)])
+def test_full_size_frames_against_oracle(pkg, gpu_ctx, oracle, w, h):
+    """BASELINE configs 3 and 4 at their real frame sizes (uniform ray-angle
+    tables): two frames, every feature, float and 16 bit."""
+    k = kinect_scaled(w, h)
+    set_k(gpu_ctx, k)
+    frames = np.stack([oracle.synth_depth(0xD2C00003, f, w, h) for f in range(2)])
+    f32 = gpu_all_features(pkg, gpu_ctx, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_F32)
+    u16 = gpu_all_features(pkg, gpu_ctx, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)
+    i = 1
+    rng = oracle.laserscan(frames[i], k)
+    for f, name in FEATURE_NAMES.items():
+        want = oracle.feature(f, rng, k)
+        assert_float_parity(name, f32[name][i], want)
+        assert_u16_parity(name, u16[name][i], oracle.quantise(f, want, rng))
+    assert_u16_parity("range", u16["range_fused"][i], oracle.quantise(0, rng, rng))
+
+
+def test_large_batch_properties(pkg, gpu_ctx, oracle):
+    """BASELINE config 2 batch size (256 frames of 960x540) through the host API:
+    size-independent properties instead of a 256-frame oracle run."""
+    w, h, n = 960, 540, 256
+    k = kinect_scaled(w, h)
+    set_k(gpu_ctx, k)
+    base = np.stack([oracle.synth_depth(0xD2C00002, f, w, h) for f in range(4)])
+    frames = np.concatenate([base] * (n // 4))
+    outs = gpu_ctx.convert(pkg.DC_BEARING, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16, want=(True,) * 4)
+    fl = gpu_ctx.convert(pkg.DC_FLEXION, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)[0]
+    for o in outs + [fl]:
+        o = o.reshape(n // 4, 4, h, w)
+        assert (o == o[0]).all()  # identical frames give identical images wherever they sit
+    rng = oracle.laserscan(base[2], k)
+    for d in range(4):
+        want = oracle.quantise(F_BEARING_H + d, oracle.feature(F_BEARING_H + d, rng, k), rng)
+        assert_u16_parity("bearing", outs[d][254], want)
+        # invalid-depth mask (depth_to_bearing.h:204-207): zero depth -> exactly 0
+        assert not outs[d][254][base[2] == 0].any()
+    assert_u16_parity("flexion", fl[254], oracle.cli_frame(F_FLEXION, 0, base[2], k)[2])
+    # border stays 0 (depth_to_flexion.h:156-161)
+    assert not fl[:, 0].any() and not fl[:, -1].any() and not fl[:, :, 0].any() and not fl[:, :, -1].any()
