@@ -356,9 +356,14 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT>())
     const long long gid      = (long long)blockIdx.x * kPairThreads + threadIdx.x;
     const int       gx       = int(gid % groups_x);
     const long long t        = gid / groups_x;
-    const int       strip    = int(t % strips);
-    const long long fp       = t / strips;
-    if (2 * fp >= n_frames)
+    // Frame pair varies faster than the strip: the CTAs resident at any moment
+    // cover all frames of a few strips, so a table row is fetched from HBM once
+    // per launch and then hit in L2 by every frame pair (with the strip fastest,
+    // the 1 GB of streamed output evicted the 8-35 MB tables between pairs).
+    const int       pairs    = (n_frames + 1) >> 1;
+    const long long fp       = t % pairs;
+    const int       strip    = int(t / pairs);
+    if (strip >= strips)
         return;
     const long long fa = 2 * fp, fb = min(fa + 1, (long long)n_frames - 1);
     const int  u0 = gx * 4, w = p.w, h = p.h;
@@ -558,9 +563,14 @@ __global__ void __launch_bounds__(kPairThreads, DC_FLEX_BLOCKS)
     const long long gid      = (long long)blockIdx.x * kPairThreads + threadIdx.x;
     const int       gx       = int(gid % groups_x);
     const long long t        = gid / groups_x;
-    const int       strip    = int(t % strips);
-    const long long fp       = t / strips;
-    if (2 * fp >= n_frames)
+    // Frame pair varies faster than the strip: the CTAs resident at any moment
+    // cover all frames of a few strips, so a table row is fetched from HBM once
+    // per launch and then hit in L2 by every frame pair (with the strip fastest,
+    // the 1 GB of streamed output evicted the 8-35 MB tables between pairs).
+    const int       pairs    = (n_frames + 1) >> 1;
+    const long long fp       = t % pairs;
+    const int       strip    = int(t / pairs);
+    if (strip >= strips)
         return;
     const long long fa = 2 * fp, fb = min(fa + 1, (long long)n_frames - 1);
     const int u0 = gx * 2, w = p.w, h = p.h;
