@@ -258,6 +258,29 @@ constexpr bool has_pair_kernel() {
 
 // The frame-pair row-marching kernels (dc_pair_kernels.cuh): u16 input,
 // width % 4 == 0, aligned frames, per-camera range proof.
+// What is known about a job before the launch (dc_pair.cuh SPEC_*): with all
+// outputs wanted and the camera tables of the feature either all per-pixel
+// arrays or all scalars, the row loop is compiled without pointer tests.
+template <int FEAT, int IN>
+int pair_spec(const dc::kparams& p) {
+    if (IN == dc::IN_U16_DEPTH && p.range_factor.p == nullptr)
+        return dc::pr::SPEC_GENERIC;
+    int tables = 0, scalars = 0;
+    auto see = [&](const dc::tab_ref& t) { (t.p != nullptr ? tables : scalars) += 1; };
+    if (FEAT == dc::FEAT_BEARING || FEAT == dc::FEAT_MAX_CURVE) {
+        for (int d = 0; d < 4; ++d) {
+            if (FEAT == dc::FEAT_BEARING && p.out[d] == nullptr)
+                return dc::pr::SPEC_GENERIC;
+            see(p.cosp[d]);
+        }
+    } else if (FEAT == dc::FEAT_CURVATURE) {
+        if (p.out[0] == nullptr || p.out[1] == nullptr)
+            return dc::pr::SPEC_GENERIC;
+        see(p.d_phi), see(p.d_theta), see(p.d_phi_theta);
+    }
+    return scalars == 0 ? dc::pr::SPEC_TABLES : tables == 0 ? dc::pr::SPEC_UNIFORM : dc::pr::SPEC_GENERIC;
+}
+
 template <int FEAT, int IN, int OUT>
 cudaError_t launch_pair(const dc::kparams& p, int n_frames, cudaStream_t s) {
     const int       rps    = rows_per_strip();
@@ -267,8 +290,23 @@ cudaError_t launch_pair(const dc::kparams& p, int n_frames, cudaStream_t s) {
     const long long blocks  = (threads + dc::pr::kPairThreads - 1) / dc::pr::kPairThreads;
     if (blocks > 0x7fffffffLL)
         return cudaErrorInvalidConfiguration;
-    dc::pr::pair_kernel<FEAT, IN, OUT>
-        <<<unsigned(blocks), dc::pr::kPairThreads, dc::pr::pair_smem_bytes<FEAT>(), s>>>(p, n_frames, rps);
+    const dim3   grid{unsigned(blocks)}, block{unsigned(dc::pr::kPairThreads)};
+    const size_t smem = dc::pr::pair_smem_bytes<FEAT>();
+    static const int forced = [] {
+        const char* e = std::getenv("DC_PAIR_SPEC");  // debugging: 0 forces the generic kernel
+        return e != nullptr ? std::atoi(e) : -1;
+    }();
+    const int spec = forced == 0 ? 0 : pair_spec<FEAT, IN>(p);
+    switch (spec) {
+    case dc::pr::SPEC_TABLES:
+        dc::pr::pair_kernel<FEAT, IN, OUT, dc::pr::SPEC_TABLES><<<grid, block, smem, s>>>(p, n_frames, rps);
+        break;
+    case dc::pr::SPEC_UNIFORM:
+        dc::pr::pair_kernel<FEAT, IN, OUT, dc::pr::SPEC_UNIFORM><<<grid, block, smem, s>>>(p, n_frames, rps);
+        break;
+    default:
+        dc::pr::pair_kernel<FEAT, IN, OUT, dc::pr::SPEC_GENERIC><<<grid, block, smem, s>>>(p, n_frames, rps);
+    }
     return cudaGetLastError();
 }
 

@@ -141,6 +141,47 @@ __device__ __forceinline__ void cp_async(void* smem_dst, const void* gsrc, bool 
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
+// SPEC: what the launch code has already established about a job, so that the
+// row loop carries no pointer tests. At run time those tests cost ~60
+// instructions per row and, worse, split the loop body into one basic block per
+// output (ptxas does not schedule across the uniform branches: 4 independent
+// dependency chains in flight instead of 16).
+//   SPEC_GENERIC  nothing known: every table / output pointer is tested
+//   SPEC_TABLES   every output of the feature is wanted, every camera table of
+//                 the feature is a per-pixel array (and, for depth input, so is
+//                 the range factor)
+//   SPEC_UNIFORM  every output is wanted, every angle table is one scalar (the
+//                 clamp of camera_models/utility.h:39-45, 1080p and larger);
+//                 the range factor of depth input is still an array
+enum { SPEC_GENERIC = 0, SPEC_TABLES = 1, SPEC_UNIFORM = 2 };
+template <int SPEC>
+__device__ __forceinline__ bool is_table(const tab_ref& t) {
+    if constexpr (SPEC == SPEC_TABLES)
+        return true;
+    else if constexpr (SPEC == SPEC_UNIFORM)
+        return false;
+    else
+        return t.p != nullptr;
+}
+template <int SPEC>
+__device__ __forceinline__ bool wanted(const void* out) {
+    if constexpr (SPEC != SPEC_GENERIC)
+        return true;
+    else
+        return out != nullptr;
+}
+// range factor: FAC_RUNTIME tests lane::fac, FAC_TABLE / FAC_NONE know
+enum { FAC_RUNTIME = 0, FAC_TABLE = 1, FAC_NONE = 2 };
+template <int FAC>
+__device__ __forceinline__ bool has_fac(const float* fac) {
+    if constexpr (FAC == FAC_TABLE)
+        return true;
+    else if constexpr (FAC == FAC_NONE)
+        return false;
+    else
+        return fac != nullptr;
+}
+
 constexpr int kRawSlots = 4;
 // slot 0: 4 px of frame A | 4 px of frame B        (u16 x 8)
 // slot 1: the u16 pairs holding column u0-1 of A, of B, column u0+4 of A, of B
@@ -168,7 +209,7 @@ struct lane {
 
 // Starts the copies of input row `roff / w` (roff = row * w, row clamped into
 // the image; `in` false = outside: zero-fill) into raw slots st[0..3*stride].
-template <bool RIGHT>
+template <bool RIGHT, int FAC = FAC_RUNTIME>
 __device__ __forceinline__ void issue_raw(const lane& L, int roff, bool in, uint4* st,
                                           int stride) {
     const bool l = in && L.hl, rt = in && L.hr;
@@ -184,7 +225,7 @@ __device__ __forceinline__ void issue_raw(const lane& L, int roff, bool in, uint
         cp_async<4>(s1 + 8, a + L.offr, rt);
         cp_async<4>(s1 + 12, b + L.offr, rt);
     }
-    if (L.fac != nullptr) {
+    if (has_fac<FAC>(L.fac)) {
         char*        s3 = reinterpret_cast<char*>(st + 3 * stride);
         const float* f  = L.fac + roff;
         cp_async<16>(st + 2 * stride, f, in);
@@ -194,7 +235,7 @@ __device__ __forceinline__ void issue_raw(const lane& L, int roff, bool in, uint
     }
 }
 
-template <bool RIGHT>
+template <bool RIGHT, int FAC = FAC_RUNTIME>
 __device__ __forceinline__ rawrow fetch_raw(const lane& L, float uniform_factor, const uint4* st,
                                             int stride) {
     rawrow      x;
@@ -203,7 +244,7 @@ __device__ __forceinline__ rawrow fetch_raw(const lane& L, float uniform_factor,
     x.b            = make_uint2(ab.z, ab.w);
     x.la = hl.x, x.lb = hl.y;
     x.ra = RIGHT ? hl.z : 0u, x.rb = RIGHT ? hl.w : 0u;
-    if (L.fac != nullptr) {
+    if (has_fac<FAC>(L.fac)) {
         x.f             = *reinterpret_cast<const float4*>(st + 2 * stride);
         const float4 fe = *reinterpret_cast<const float4*>(st + 3 * stride);
         x.fl = fe.x, x.fr = fe.y;
@@ -283,17 +324,20 @@ __device__ __forceinline__ void store4(void* base, size_t oa, size_t ob, const f
 
 // per-row camera table values: 4 columns -> one slot; uniform tables are
 // passed by value and need no copy. `off` = row * w + u0 (clamped into the table).
+template <int SPEC = SPEC_GENERIC>
 __device__ __forceinline__ void issue_tab4(const tab_ref& t, int off, bool in, uint4* slot) {
-    if (t.p != nullptr)
+    if (is_table<SPEC>(t))
         cp_async<16>(slot, t.p + off, in);
 }
+template <int SPEC = SPEC_GENERIC>
 __device__ __forceinline__ float4 fetch_tab4(const tab_ref& t, const uint4* slot) {
-    if (t.p == nullptr)
+    if (!is_table<SPEC>(t))
         return make_float4(t.value, t.value, t.value, t.value);
     return *reinterpret_cast<const float4*>(slot);
 }
+template <int SPEC = SPEC_GENERIC>
 __device__ __forceinline__ void issue_tab1(const tab_ref& t, int off, bool in, void* dst) {
-    if (t.p != nullptr)
+    if (is_table<SPEC>(t))
         cp_async<4>(dst, t.p + off, in);
 }
 

@@ -67,7 +67,7 @@ struct tab_slots {
 
 // Starts the copies of the camera tables that row `v` of the feature needs
 // into the thread's table slots st[0], st[stride], ... `off` = v * w + u0.
-template <int FEAT>
+template <int FEAT, int SPEC>
 __device__ __forceinline__ void issue_tabs(const kparams& p, int v, int off, int u0, uint4* st,
                                            int stride) {
     const int w = p.w, h = p.h;
@@ -76,8 +76,8 @@ __device__ __forceinline__ void issue_tabs(const kparams& p, int v, int off, int
         off           = in ? off : 0;
 #pragma unroll
         for (int d = 0; d < 4; ++d)
-            if (p.out[d] != nullptr)
-                issue_tab4(p.cosp[d], off, in, st + d * stride);
+            if (wanted<SPEC>(p.out[d]))
+                issue_tab4<SPEC>(p.cosp[d], off, in, st + d * stride);
     } else if constexpr (FEAT == FEAT_MAX_CURVE) {
         // depth_to_max_curve.h:113-139: all eight phi() are angles between a
         // pixel and one of its bearing "prior" neighbours (see dc_kernels.cuh):
@@ -86,55 +86,55 @@ __device__ __forceinline__ void issue_tabs(const kparams& p, int v, int off, int
         //   ant1 = phi((u+1,v+1),(u,v)) = D(u+1,v+1) (sic, :136)   ant2 = A(u+1,v-1)
         const bool in = v >= 1 && v < h - 1, more = in && u0 + 4 < w;
         off           = in ? off : w;  // rows off-w .. off+w stay inside the table
-        issue_tab4(p.cosp[0], off, in, st);
-        issue_tab4(p.cosp[1], off, in, st + stride);
-        issue_tab4(p.cosp[1], off + w, in, st + 2 * stride);
-        issue_tab4(p.cosp[2], off, in, st + 3 * stride);
-        issue_tab4(p.cosp[2], off + w, in, st + 4 * stride);
-        issue_tab4(p.cosp[3], off - w, in, st + 5 * stride);
+        issue_tab4<SPEC>(p.cosp[0], off, in, st);
+        issue_tab4<SPEC>(p.cosp[1], off, in, st + stride);
+        issue_tab4<SPEC>(p.cosp[1], off + w, in, st + 2 * stride);
+        issue_tab4<SPEC>(p.cosp[2], off, in, st + 3 * stride);
+        issue_tab4<SPEC>(p.cosp[2], off + w, in, st + 4 * stride);
+        issue_tab4<SPEC>(p.cosp[3], off - w, in, st + 5 * stride);
         char*     e  = reinterpret_cast<char*>(st + 6 * stride);
         const int o4 = more ? 4 : 0;
-        issue_tab1(p.cosp[0], off + o4, more, e);
-        issue_tab1(p.cosp[2], off + w + o4, more, e + 4);
-        issue_tab1(p.cosp[3], off - w + o4, more, e + 8);
+        issue_tab1<SPEC>(p.cosp[0], off + o4, more, e);
+        issue_tab1<SPEC>(p.cosp[2], off + w + o4, more, e + 4);
+        issue_tab1<SPEC>(p.cosp[3], off - w + o4, more, e + 8);
     } else if constexpr (FEAT == FEAT_CURVATURE) {
         const bool in = v >= 1 && v < h - 1;
         off           = in ? off : 0;
-        issue_tab4(p.d_phi, off, in, st);
-        issue_tab4(p.d_theta, off, in, st + stride);
-        issue_tab4(p.d_phi_theta, off, in, st + 2 * stride);
+        issue_tab4<SPEC>(p.d_phi, off, in, st);
+        issue_tab4<SPEC>(p.d_theta, off, in, st + stride);
+        issue_tab4<SPEC>(p.d_phi_theta, off, in, st + 2 * stride);
     }
 }
 
-template <int FEAT>
+template <int FEAT, int SPEC>
 __device__ __forceinline__ rtabs<FEAT> fetch_tabs(const kparams& p, const uint4* st, int stride) {
     rtabs<FEAT> t;
     if constexpr (FEAT == FEAT_BEARING) {
 #pragma unroll
         for (int d = 0; d < 4; ++d)
-            t.c[d] = p.out[d] != nullptr ? fetch_tab4(p.cosp[d], st + d * stride)
+            t.c[d] = wanted<SPEC>(p.out[d]) ? fetch_tab4<SPEC>(p.cosp[d], st + d * stride)
                                          : make_float4(.5f, .5f, .5f, .5f);
     } else if constexpr (FEAT == FEAT_MAX_CURVE) {
-        put4(t.cH, fetch_tab4(p.cosp[0], st));
-        put4(t.cV0, fetch_tab4(p.cosp[1], st + stride));
-        put4(t.cV1, fetch_tab4(p.cosp[1], st + 2 * stride));
-        put4(t.cD0, fetch_tab4(p.cosp[2], st + 3 * stride));
-        put4(t.cD1, fetch_tab4(p.cosp[2], st + 4 * stride));
-        put4(t.cA, fetch_tab4(p.cosp[3], st + 5 * stride));
+        put4(t.cH, fetch_tab4<SPEC>(p.cosp[0], st));
+        put4(t.cV0, fetch_tab4<SPEC>(p.cosp[1], st + stride));
+        put4(t.cV1, fetch_tab4<SPEC>(p.cosp[1], st + 2 * stride));
+        put4(t.cD0, fetch_tab4<SPEC>(p.cosp[2], st + 3 * stride));
+        put4(t.cD1, fetch_tab4<SPEC>(p.cosp[2], st + 4 * stride));
+        put4(t.cA, fetch_tab4<SPEC>(p.cosp[3], st + 5 * stride));
         const float4 e = *reinterpret_cast<const float4*>(st + 6 * stride);
-        t.cH[4]        = p.cosp[0].p != nullptr ? e.x : p.cosp[0].value;
-        t.cD1[4]       = p.cosp[2].p != nullptr ? e.y : p.cosp[2].value;
-        t.cA[4]        = p.cosp[3].p != nullptr ? e.z : p.cosp[3].value;
+        t.cH[4]        = is_table<SPEC>(p.cosp[0]) ? e.x : p.cosp[0].value;
+        t.cD1[4]       = is_table<SPEC>(p.cosp[2]) ? e.y : p.cosp[2].value;
+        t.cA[4]        = is_table<SPEC>(p.cosp[3]) ? e.z : p.cosp[3].value;
     } else if constexpr (FEAT == FEAT_CURVATURE) {
-        t.phi   = fetch_tab4(p.d_phi, st);
-        t.theta = fetch_tab4(p.d_theta, st + stride);
-        t.pt    = fetch_tab4(p.d_phi_theta, st + 2 * stride);
+        t.phi   = fetch_tab4<SPEC>(p.d_phi, st);
+        t.theta = fetch_tab4<SPEC>(p.d_theta, st + stride);
+        t.pt    = fetch_tab4<SPEC>(p.d_phi_theta, st + 2 * stride);
     }
     return t;
 }
 
 // ---- bearing: conversion/depth_to_bearing.h:185-214 ------------------------
-template <int OUT>
+template <int OUT, int SPEC>
 __device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BEARING>& up,
                                             const wrow<FEAT_BEARING>& mid,
                                             const wrow<FEAT_BEARING>& dn,
@@ -145,7 +145,7 @@ __device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BE
         sm[i] = mul2(mid.r[i], mid.r[i]);
 #pragma unroll
     for (int d = 0; d < 4; ++d) {
-        if (p.out[d] == nullptr)
+        if (!wanted<SPEC>(p.out[d]))
             continue;
         const float cs[4] = {tb.c[d].x, tb.c[d].y, tb.c[d].z, tb.c[d].w};
         f2          o[4];
@@ -241,7 +241,7 @@ struct curv_consts {
     float q_div, q_rcp;  // hi - lo and its refined reciprocal (u16 output)
 };
 
-template <int OUT>
+template <int OUT, int SPEC>
 __device__ __forceinline__ void curvature_row(const kparams& p, const wrow<FEAT_CURVATURE>& up,
                                               const wrow<FEAT_CURVATURE>& mid,
                                               const wrow<FEAT_CURVATURE>& dn,
@@ -278,7 +278,7 @@ __device__ __forceinline__ void curvature_row(const kparams& p, const wrow<FEAT_
         const float mnb = fminf(fminf(up.m3[i].y, mid.m3[i].y), dn.m3[i].y);
         const bool  oka = mna != 0.0f, okb = mnb != 0.0f;
         f2          kg = B(0.0f), km = B(0.0f);
-        if (p.out[0] != nullptr) {
+        if (wanted<SPEC>(p.out[0])) {
             const f2 n = sub2(mul2(f_uu, f_vv), mul2(f_uv, f_uv));
             kg         = div2_fast(n, dd);
             // n can be -0 (f_uu < 0, f_vv = f_uv = +0); the residual step
@@ -286,7 +286,7 @@ __device__ __forceinline__ void curvature_row(const kparams& p, const wrow<FEAT_
             kg = make_float2(n.x == 0.0f ? n.x : kg.x, n.y == 0.0f ? n.y : kg.y);
             kg         = make_float2(oka ? kg.x : 0.0f, okb ? kg.y : 0.0f);
         }
-        if (p.out[1] != nullptr) {
+        if (wanted<SPEC>(p.out[1])) {
             const f2 t0  = mul2(add2(B(1.0f), fv2), f_uu);
             const f2 t1  = mul2(mul2(add2(f_u, f_u), f_v), f_uv);
             const f2 t2  = mul2(add2(B(1.0f), fu2), f_vv);
@@ -327,9 +327,9 @@ __device__ __forceinline__ void curvature_row(const kparams& p, const wrow<FEAT_
             m[i] = km;
         }
     }
-    if (p.out[0] != nullptr)
+    if (wanted<SPEC>(p.out[0]))
         store4<OUT>(p.out[0], at.oa, at.ob, g);
-    if (p.out[1] != nullptr)
+    if (wanted<SPEC>(p.out[1]))
         store4<OUT>(p.out[1], at.oa, at.ob, m);
 }
 
@@ -348,7 +348,7 @@ constexpr size_t pair_smem_bytes() {
     return size_t(2) * (kRawSlots + tab_slots<FEAT>::n) * kPairThreads * sizeof(uint4);
 }
 
-template <int FEAT, int IN, int OUT>
+template <int FEAT, int IN, int OUT, int SPEC>
 __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT>())
     pair_kernel(const __grid_constant__ kparams p, int n_frames, int rows_per_strip) {
     const int       groups_x = p.w >> 2;
@@ -369,6 +369,7 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT>())
     const int  u0 = gx * 4, w = p.w, h = p.h;
     const int  v0 = strip * rows_per_strip, v1 = min(v0 + rows_per_strip, h);
     constexpr bool R = feat_traits<FEAT>::right;
+    constexpr int  FC = IN != IN_U16_DEPTH ? FAC_NONE : SPEC != SPEC_GENERIC ? FAC_TABLE : FAC_RUNTIME;
     lane L;
     L.A   = static_cast<const unsigned short*>(p.in) + size_t(fa) * p.frame_px + u0;
     L.Bf  = static_cast<const unsigned short*>(p.in) + size_t(fb) * p.frame_px + u0;
@@ -393,14 +394,14 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT>())
     uint4* const  stg1  = smem + NSLOT * T + threadIdx.x;
 
     wrow<FEAT> up, mid, dn;
-    issue_raw<R>(L, max(v0 - 1, 0) * w, v0 >= 1, stg0, T);
-    issue_raw<R>(L, v0 * w, true, stg1, T);
+    issue_raw<R, FC>(L, max(v0 - 1, 0) * w, v0 >= 1, stg0, T);
+    issue_raw<R, FC>(L, v0 * w, true, stg1, T);
     cp_async_commit();
     cp_async_wait_all();
-    commit<FEAT, IN>(fetch_raw<R>(L, ufac, stg0, T), up);
-    commit<FEAT, IN>(fetch_raw<R>(L, ufac, stg1, T), mid);
-    issue_raw<R>(L, min(v0 + 1, h - 1) * w, v0 + 1 < h, stg0, T);
-    issue_tabs<FEAT>(p, v0, v0 * w + u0, u0, stg0 + kRawSlots * T, T);
+    commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, stg0, T), up);
+    commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, stg1, T), mid);
+    issue_raw<R, FC>(L, min(v0 + 1, h - 1) * w, v0 + 1 < h, stg0, T);
+    issue_tabs<FEAT, SPEC>(p, v0, v0 * w + u0, u0, stg0 + kRawSlots * T, T);
     cp_async_commit();
 
     pos at;
@@ -419,12 +420,12 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT>())
         uint4* const sn = cur ? stg0 : stg1;
         cur ^= 1;
         cp_async_wait_all();
-        commit<FEAT, IN>(fetch_raw<R>(L, ufac, sc, T), dn);
-        const rtabs<FEAT> tb = fetch_tabs<FEAT>(p, sc + kRawSlots * T, T);
+        commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, sc, T), dn);
+        const rtabs<FEAT> tb = fetch_tabs<FEAT, SPEC>(p, sc + kRawSlots * T, T);
         {
             const bool in2 = v + 2 < h;
-            issue_raw<R>(L, in2 ? roff + w : roff - w, in2, sn, T);
-            issue_tabs<FEAT>(p, v + 1, roff + u0, u0, sn + kRawSlots * T, T);
+            issue_raw<R, FC>(L, in2 ? roff + w : roff - w, in2, sn, T);
+            issue_tabs<FEAT, SPEC>(p, v + 1, roff + u0, u0, sn + kRawSlots * T, T);
             cp_async_commit();
         }
         at.v               = v;
@@ -433,11 +434,11 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT>())
         for (int i = 0; i < 4; ++i)
             at.inside[i] = col_in[i] * row_in;
         if constexpr (FEAT == FEAT_BEARING)
-            bearing_row<OUT>(p, up, mid, dn, tb, at);
+            bearing_row<OUT, SPEC>(p, up, mid, dn, tb, at);
         else if constexpr (FEAT == FEAT_MAX_CURVE)
             max_curve_row<OUT>(p, up, mid, dn, tb, at);
         else if constexpr (FEAT == FEAT_CURVATURE)
-            curvature_row<OUT>(p, up, mid, dn, tb, at, cc);
+            curvature_row<OUT, SPEC>(p, up, mid, dn, tb, at, cc);
         up  = mid;
         mid = dn;
         roff += w;

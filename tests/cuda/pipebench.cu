@@ -54,19 +54,27 @@ __device__ __forceinline__ float rsq(float a) {
     return d;
 }
 
+__constant__ float k_nz = -0.0f;
+__device__ __forceinline__ float2 un(u64 v) {
+    float2 r;
+    asm("mov.b64 {%0,%1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
+    return r;
+}
 constexpr int CH = 8;  // independent chains per thread
 
 template <int MODE>
-__global__ void __launch_bounds__(512) bench(float* out, int iters, long long* cyc) {
-    float x[CH], y[CH];
-    u64   p[CH], q[CH];
+__global__ void __launch_bounds__(512, 1) bench(float* out, int iters, long long* cyc) {
+    float x[CH], y[CH], z[CH];
+    u64   p[CH], q[CH], r[CH];
     const float s = 1.0f + threadIdx.x * 1e-7f, t = 0.5f;
 #pragma unroll
     for (int i = 0; i < CH; ++i) {
         x[i] = s + i;
-        y[i] = t + i;
+        y[i] = s * 0.5f + i;
+        z[i] = s * 0.3f + i;
         p[i] = pk(x[i], y[i]);
         q[i] = pk(y[i], x[i]);
+        r[i] = pk(y[i] * 0.25f, x[i] * 0.125f);
     }
     const u64 cs = pk(s, s), ct = pk(t, t);
     __syncthreads();
@@ -87,6 +95,33 @@ __global__ void __launch_bounds__(512) bench(float* out, int iters, long long* c
             if (MODE == 10) { x[i] = rsq(x[i]); p[i] = fma2(p[i], cs, ct); q[i] = fma2(q[i], ct, cs); y[i] = fmnmx(y[i], s); }
             if (MODE == 11) { x[i] = ffma(x[i], s, t); y[i] = ffma(y[i], t, s); }          // 2 scalar FFMA chains
             if (MODE == 12) { p[i] = fma2(p[i], cs, ct); x[i] = ffma(x[i], s, t); }        // FFMA2 + FFMA
+            // operand forms of FFMA2 as the product kernels use them (C intrinsics)
+            if (MODE == 13) { float2 r = __ffma2_rn(un(p[i]), un(cs), make_float2(k_nz, k_nz)); p[i] = pk(r.x, r.y); }  // c = UR.F32
+            if (MODE == 14) { float2 r = __ffma2_rn(un(p[i]), make_float2(s, s), un(ct)); p[i] = pk(r.x, r.y); }      // b = R.F32 broadcast
+            if (MODE == 15) { float2 r = __ffma2_rn(un(p[i]), un(cs), make_float2(0.0878f, 0.0878f)); p[i] = pk(r.x, r.y); }  // c = immediate
+            if (MODE == 16) { float2 r = __ffma2_rn(un(p[i]), make_float2(s, s), make_float2(k_nz, k_nz)); p[i] = pk(r.x, r.y); }  // b = R.F32, c = UR.F32
+            if (MODE == 17) { float2 r = __ffma2_rn(un(p[i]), un(p[i]), make_float2(k_nz, k_nz)); p[i] = pk(r.x, r.y); }  // square, c = UR.F32
+            // register operand patterns (4 warps per SMSP, as the product kernels run)
+            if (MODE == 19) p[i] = fma2(p[i], q[i], r[i]);                       // three distinct register pairs
+            if (MODE == 20) p[i] = fma2(p[i], p[i], r[i]);                       // a == b
+            if (MODE == 21) { float2 v = __ffma2_rn(un(p[i]), un(q[i]), make_float2(k_nz, k_nz)); p[i] = pk(v.x, v.y); }  // a, b distinct, c = UR
+            if (MODE == 22) { float2 v = __ffma2_rn(un(p[i]), un(q[i]), make_float2(0.0878f, 0.0878f)); p[i] = pk(v.x, v.y); }  // c = imm
+            if (MODE == 23) { float2 v = __ffma2_rn(un(p[i]), make_float2(x[i], x[i]), un(r[i])); p[i] = pk(v.x, v.y); }  // b = R.F32 broadcast, distinct
+            if (MODE == 24) p[i] = add2(p[i], q[i]);                              // FADD2 distinct
+            if (MODE == 25) { p[i] = fma2(p[i], q[i], r[i]); q[i] = fma2(q[i], r[i], p[i]); }  // rotating operands, no reuse
+            if (MODE == 26) x[i] = ffma(x[i], y[i], s);                           // scalar FFMA distinct
+            if (MODE == 27) { float2 v = __ffma2_rn(un(p[i]), make_float2(x[i], x[i]), make_float2(k_nz, k_nz)); p[i] = pk(v.x, v.y); }  // b = R.F32 varying, c = UR
+            if (MODE == 28) x[i] = ffma(x[i], y[i], z[i]);                        // scalar, three distinct
+            if (MODE == 29) { float2 v = __ffma2_rn(un(p[i]), make_float2(0.0878f, 0.0878f), un(r[i])); p[i] = pk(v.x, v.y); }  // b = imm, a, c distinct
+            if (MODE == 30) { float2 a = un(p[i]), b = un(q[i]), c = un(r[i]);    // the packed op as two scalar FFMAs on register pairs
+                              p[i] = pk(ffma(a.x, b.x, c.x), ffma(a.y, b.y, c.y)); }
+            if (MODE == 31) { float2 a = un(p[i]), b = un(q[i]);                  // two scalar FMULs on register pairs
+                              p[i] = pk(fmul(a.x, b.x), fmul(a.y, b.y)); }
+            if (MODE == 32) { float2 a = un(p[i]); p[i] = pk(ffma(a.x, x[i], t), ffma(a.y, x[i], t)); }  // scalar pair, shared b
+            if (MODE == 33) { p[i] = fma2(p[i], q[i], r[i]); x[i] = ffma(x[i], y[i], z[i]); y[i] = fmnmx(y[i], s); }  // FFMA2 + FFMA + ALU, distinct
+            if (MODE == 34) { float2 a = un(p[i]), b = un(q[i]), c = un(r[i]);    // 2 scalar + 1 ALU
+                              p[i] = pk(ffma(a.x, b.x, c.x), ffma(a.y, b.y, c.y)); y[i] = fmnmx(y[i], s); }
+            if (MODE == 18) { x[i] = rsq(x[i]); y[i] = rsq(y[i]); p[i] = fma2(p[i], cs, ct); q[i] = fma2(q[i], ct, cs); }  // 2 MUFU back to back + 2 FFMA2
         }
     }
     const long long c1 = clock64();
@@ -96,7 +131,7 @@ __global__ void __launch_bounds__(512) bench(float* out, int iters, long long* c
         float a, b, c, d;
         asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(p[i]));
         asm("mov.b64 {%0,%1}, %2;" : "=f"(c), "=f"(d) : "l"(q[i]));
-        acc += x[i] + y[i] + a + b + c + d;
+        acc += x[i] + y[i] + z[i] + a + b + c + d + un(r[i]).x;
     }
     out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
     if (threadIdx.x == 0 && blockIdx.x == 0) *cyc = c1 - c0;
@@ -104,7 +139,8 @@ __global__ void __launch_bounds__(512) bench(float* out, int iters, long long* c
 
 template <int MODE>
 void run(const char* name, int inst_per_chain, int lanes_per_chain) {
-    const int  blocks = 148 * 2, threads = 512, iters = 4096;
+    // one 512-thread CTA per SM: 4 warps per SMSP
+    const int  blocks = 148, threads = 512, iters = 4096;
     float*     out;
     long long* cyc;
     cudaMalloc(&out, sizeof(float) * blocks * threads);
@@ -121,11 +157,10 @@ void run(const char* name, int inst_per_chain, int lanes_per_chain) {
     cudaEventElapsedTime(&ms, a, b);
     long long c;
     cudaMemcpy(&c, cyc, 8, cudaMemcpyDeviceToHost);
-    // warps per SMSP: 2 blocks * 16 warps / 4 SMSP = 8
-    const double winst_smsp = 8.0 * iters * CH * inst_per_chain;
+    const double winst_smsp = 4.0 * iters * CH * inst_per_chain;
     const double ipc        = winst_smsp / double(c);
-    printf("%-28s %8.3f ms  cycles %9lld  warp-inst/clk/SMSP %.3f  fp32 lane-ops/clk/SM %.1f\n", name,
-           ms, c, ipc, ipc * 4 * 32 * lanes_per_chain / inst_per_chain);
+    printf("%-28s %8.3f ms  cycles %9lld  clk/warp-inst/SMSP %.3f  fp32 lane-ops/clk/SM %.1f\n", name,
+           ms, c, 1.0 / ipc, ipc * 4 * 32 * lanes_per_chain / inst_per_chain);
     cudaFree(out);
     cudaFree(cyc);
 }
@@ -144,5 +179,27 @@ int main() {
     run<8>("2 FFMA2 + FMNMX", 3, 4);
     run<9>("MUFU.RSQ", 1, 1);
     run<10>("RSQ + 2 FFMA2 + FMNMX", 4, 4);
+    run<13>("FFMA2 c=UR.F32", 1, 2);
+    run<14>("FFMA2 b=R.F32 bcast", 1, 2);
+    run<15>("FFMA2 c=imm", 1, 2);
+    run<16>("FFMA2 b=R.F32 c=UR.F32", 1, 2);
+    run<17>("FFMA2 square c=UR.F32", 1, 2);
+    run<18>("2 RSQ + 2 FFMA2", 4, 6);
+    run<19>("FFMA2 a,b,c distinct", 1, 2);
+    run<20>("FFMA2 a==b, c distinct", 1, 2);
+    run<21>("FFMA2 a,b distinct c=UR", 1, 2);
+    run<22>("FFMA2 a,b distinct c=imm", 1, 2);
+    run<23>("FFMA2 b=R.F32 distinct", 1, 2);
+    run<24>("FADD2 distinct", 1, 2);
+    run<25>("FFMA2 rotating operands", 2, 4);
+    run<26>("FFMA a,b distinct", 1, 1);
+    run<27>("FFMA2 b=R.F32 varying c=UR", 1, 2);
+    run<28>("FFMA a,b,c distinct", 1, 1);
+    run<29>("FFMA2 b=imm a,c distinct", 1, 2);
+    run<30>("2x FFMA on pairs distinct", 2, 2);
+    run<31>("2x FMUL on pairs distinct", 2, 2);
+    run<32>("2x FFMA pair, shared b", 2, 2);
+    run<33>("FFMA2+FFMA+FMNMX distinct", 3, 3);
+    run<34>("2x FFMA + FMNMX", 3, 2);
     return 0;
 }
