@@ -8,15 +8,38 @@
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
+#include <cstdio>
+#include <cstdlib>
 #include <deque>
 #include <functional>
 #include <mutex>
 #include <thread>
 
+#include <sys/resource.h>
+#include <sys/syscall.h>
+#include <unistd.h>
+
 namespace sens_loc::apps {
 namespace {
 
 namespace png = sens_loc::io::png;
+
+void prof(const char* what, int a = -1) { profile_mark(what, a); }
+}  // namespace
+
+// DEPTH2X_PROFILE=1: stage timestamps on stderr (seconds since the first call)
+void profile_mark(const char* what, int a) {
+    static const bool on = std::getenv("DEPTH2X_PROFILE") != nullptr;
+    if (!on)
+        return;
+    static const auto t0 = std::chrono::steady_clock::now();
+    static std::mutex m;
+    const double      t = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    std::lock_guard<std::mutex> l(m);
+    std::fprintf(stderr, "[profile %8.4f s] %s %d\n", t, what, a);
+}
+
+namespace {
 
 // ---- a persistent thread pool with a blocking parallel_for -------------------
 class pool {
@@ -49,6 +72,8 @@ class pool {
 
   private:
     void work() {
+        // codec workers yield to the thread that initialises CUDA and feeds the GPU
+        setpriority(PRIO_PROCESS, static_cast<id_t>(syscall(SYS_gettid)), 5);
         const int    me = _ids++;
         std::uint64_t seen = 0;
         std::unique_lock<std::mutex> l(_m);
@@ -102,22 +127,32 @@ class channel {
     std::deque<T>           _q;
 };
 
-struct pinned {
+// Batch buffers are ordinary page-aligned memory: dc_convert_host stages
+// pageable memory through the context's own pinned ring (one memcpy per chunk on
+// the otherwise idle GPU thread), whereas pinning 100-500 MB per buffer up front
+// costs 0.1 s each on the reader's critical path, which dominates short jobs.
+struct hostbuf {
     void*       p   = nullptr;
     std::size_t cap = 0;
     bool reserve(std::size_t bytes) {
         if (cap >= bytes)
             return true;
-        dc_host_free(p);
-        p   = dc_host_alloc(bytes);
-        cap = p != nullptr ? bytes : 0;
+        std::free(p);
+        p = nullptr;
+        const std::size_t rounded = (bytes + 4095) & ~std::size_t(4095);
+        if (posix_memalign(&p, 4096, rounded) != 0)
+            p = nullptr;
+        cap = p != nullptr ? rounded : 0;
         return p != nullptr;
     }
-    ~pinned() { dc_host_free(p); }
+    hostbuf() = default;
+    hostbuf(const hostbuf&)            = delete;
+    hostbuf& operator=(const hostbuf&) = delete;
+    ~hostbuf() { std::free(p); }
 };
 
 struct batch {
-    pinned           in, out[DC_MAX_OUTPUTS];
+    hostbuf          in, out[DC_MAX_OUTPUTS];
     std::vector<int> idx;  // index of the frame in slot k
     int              w = 0, h = 0;
     bool             last = false, gpu_ok = true;
@@ -145,8 +180,14 @@ struct pending_file {
 // One GPU: indices [first, last] through reader -> gpu -> writer.
 void run_device(const convert_spec& spec, int device, int first, int last, int batch_size,
                 int threads, shared_state& st) {
+    // The context is created before any codec thread starts: cuInit next to 16
+    // threads first-touching their buffers takes 1.3 s instead of 0.6 s (measured;
+    // both sides hammer the address-space lock).
     dc_ctx* ctx = nullptr;
-    if (dc_create(device, &ctx) != DC_OK) {
+    prof("dc_create begin", device);
+    const bool have_ctx = dc_create(device, &ctx) == DC_OK;
+    prof("dc_create end", device);
+    if (!have_ctx) {
         {
             std::lock_guard<std::mutex> l(st.m);
             std::cerr << console::err() << "GPU " << device << ": " << dc_last_error(nullptr) << "\n";
@@ -159,12 +200,15 @@ void run_device(const convert_spec& spec, int device, int first, int last, int b
     for (const auto& o : spec.output)
         n_out += !o.empty();
 
-    constexpr int   kBuffers = 3;
+    constexpr int   kBuffers = 4;
     batch           buffers[kBuffers];
     channel<batch*> free_q, gpu_q, write_q;
     for (auto& b : buffers)
         free_q.push(&b);
-    pool read_pool(std::max(1, threads / 2)), write_pool(std::max(1, threads - threads / 2));
+    // Both pools get every thread: decode and encode work are unequal (bearing
+    // writes four files per frame read) and the kernel time-slices what is runnable.
+    pool read_pool(std::max(1, threads)), write_pool(std::max(1, threads));
+    const int total = last - first + 1;
 
     // ---- reader ------------------------------------------------------------
     std::thread reader([&] {
@@ -172,13 +216,16 @@ void run_device(const convert_spec& spec, int device, int first, int last, int b
         scratch.resize(std::size_t(read_pool.size()));
         int next = first;
         while (next <= last) {
-            // frames per batch: about 256 MB of pinned memory per buffer
+            // frames per batch: at most 256 MB per buffer and 64 frames, at least
+            // one frame per thread, and about six batches per job so that
+            // decoding, the GPU and encoding overlap even on short jobs
             int want = batch_size;
             if (want <= 0) {
                 const std::size_t px = spec.camera.model != 0
                                            ? std::size_t(spec.camera.w) * spec.camera.h
                                            : std::size_t(1920) * 1080;
-                want = int(std::clamp<std::size_t>((std::size_t(256) << 20) / (px * 2 * (1 + n_out)), 1, 64));
+                const int cap = int(std::clamp<std::size_t>((std::size_t(256) << 20) / (px * 2 * (1 + n_out)), 1, 64));
+                want = std::clamp(std::max((total + 5) / 6, threads), 1, cap);
             }
             const int n = std::min(want, last - next + 1);
             std::vector<pending_file> files{};
@@ -213,6 +260,7 @@ void run_device(const convert_spec& spec, int device, int first, int last, int b
                     }
                 }
             }
+            prof("files read", n);
             batch* b = free_q.pop();
             b->idx.clear();
             b->w = bw, b->h = bh;
@@ -238,6 +286,7 @@ void run_device(const convert_spec& spec, int device, int first, int last, int b
                     mem = mem && b->out[o++].reserve(std::max<std::size_t>(1, b->idx.size() * fpx * 2));
             std::vector<char> bad;
             bad.assign(std::size_t(use), 0);
+            prof("pinned ready", use);
             if (mem) {
                 // phase B: inflate + unfilter straight into the pinned batch buffer
                 read_pool.parallel_for(use, [&](int k, int worker) {
@@ -258,6 +307,7 @@ void run_device(const convert_spec& spec, int device, int first, int last, int b
                     b->idx[std::size_t(slot_of[std::size_t(k)])] = -1 - files[std::size_t(k)].idx;
                 }
             next += use;
+            prof("decoded", use);
             gpu_q.push(b);
         }
     });
@@ -292,7 +342,9 @@ void run_device(const convert_spec& spec, int device, int first, int last, int b
                             j.out[s] = b->out[o++].p;
                     j.clamp_lo = spec.clamp_lo, j.clamp_hi = spec.clamp_hi;
                     j.scale = spec.scale, j.offset = spec.offset;
+                    prof("camera set", j.n_frames);
                     rc = dc_convert_host(ctx, &j);
+                    prof("converted", j.n_frames);
                 }
                 if (rc != DC_OK) {
                     std::lock_guard<std::mutex> l(st.m);
@@ -339,6 +391,7 @@ void run_device(const convert_spec& spec, int device, int first, int last, int b
             for (int k = 0; k < n; ++k)
                 if (b->idx[std::size_t(k)] >= 0 && (bad[std::size_t(k)] || !b->gpu_ok))
                     st.fail(b->idx[std::size_t(k)]);
+            prof("encoded+written", n);
             const bool last_batch = b->last;
             free_q.push(b);
             if (last_batch)
@@ -349,7 +402,9 @@ void run_device(const convert_spec& spec, int device, int first, int last, int b
     reader.join();
     gpu.join();
     writer.join();
+    prof("pipeline drained", device);
     dc_destroy(ctx);
+    prof("context destroyed", device);
 }
 
 }  // namespace
@@ -362,9 +417,19 @@ run_stats run_batch(const convert_spec& spec, int start, int end, int devices, i
     if (threads <= 0)
         threads = int(std::max(2u, std::thread::hardware_concurrency()));
     devices = std::max(1, std::min(devices, total));
-    const int visible = dc_device_count();
-    if (visible > 0)
-        devices = std::min(devices, visible);
+    // cuInit time grows with the number of visible GPUs: expose only the ones used
+    // (unless the caller already chose).
+    if (std::getenv("CUDA_VISIBLE_DEVICES") == nullptr) {
+        std::string vis;
+        for (int g = 0; g < devices; ++g)
+            vis += (g ? "," : "") + std::to_string(g);
+        setenv("CUDA_VISIBLE_DEVICES", vis.c_str(), 0);
+    }
+    if (devices > 1) {  // (the query initialises CUDA: not on the single-GPU path)
+        const int visible = dc_device_count();
+        if (visible > 0)
+            devices = std::min(devices, visible);
+    }
 
     shared_state             st;
     const auto               t0 = std::chrono::steady_clock::now();

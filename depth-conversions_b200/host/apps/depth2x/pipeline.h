@@ -48,5 +48,8 @@ struct run_stats {
 run_stats run_batch(const convert_spec& spec, int start, int end, int devices, int batch_size,
                     int threads);
 
+/// DEPTH2X_PROFILE=1 in the environment: stage timestamps on stderr.
+void profile_mark(const char* what, int value = -1);
+
 }  // namespace sens_loc::apps
 #endif

@@ -77,7 +77,7 @@ def main():
             dt = time.perf_counter() - t0
             assert r.returncode == 0, r.stdout + r.stderr
             best = dt if best is None else min(best, dt)
-        inner = [l for l in r.stdout.splitlines() if "took" in l]
+        inner = [l.strip() for l in (r.stdout + r.stderr).splitlines() if "took" in l]
         print(json.dumps({"arm": "depth2x (B200)", "feature": feat, "size": a.size, "frames": a.frames,
                           "devices": a.devices, "wall_s": best, "frames_per_s": a.frames / best,
                           "mpix_per_s": a.frames * w * h / best / 1e6, "host_threads": ncpu,
