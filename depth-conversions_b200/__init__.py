@@ -20,8 +20,8 @@ DEPTH2X_PATH = os.path.join(HERE, "bin", "depth2x")
 
 # enums of include/depthconv_b200.h
 DC_RANGE, DC_BEARING, DC_FLEXION, DC_CURVATURE, DC_MAX_CURVE, DC_SCALE = range(6)
-DC_IN_U16_DEPTH, DC_IN_U16_RANGE, DC_IN_F32_RANGE = range(3)
-DC_OUT_F32, DC_OUT_U16 = range(2)
+DC_IN_U16_DEPTH, DC_IN_U16_RANGE, DC_IN_F32_RANGE, DC_IN_F64_RANGE = range(4)
+DC_OUT_F32, DC_OUT_U16, DC_OUT_F64 = range(3)
 DC_OK, DC_ERR_INVALID, DC_ERR_NO_DEVICE, DC_ERR_CUDA = 0, -1, -2, -3
 DC_ERR_NO_CAMERA, DC_ERR_UNSUPPORTED, DC_ERR_NOMEM = -4, -5, -6
 
@@ -30,7 +30,8 @@ EXPORTED_SYMBOLS = [
     "dc_set_pinhole", "dc_set_equirectangular", "dc_set_frame_size", "dc_width",
     "dc_height", "dc_convert_device", "dc_convert_host", "dc_synchronize",
     "dc_host_alloc", "dc_host_free", "dc_synth_depth_device", "dc_kernel_launches",
-    "dc_quantise_host",
+    "dc_quantise_host", "dc_set_pinhole_f64", "dc_set_equirectangular_f64",
+    "dc_quantise_host_f64",
 ]
 DC_Q_RANGE, DC_Q_BEARING, DC_Q_FLEXION, DC_Q_CURVATURE, DC_Q_MAX_CURVE = range(5)
 
@@ -84,14 +85,20 @@ def lib():
                                             C.c_void_p, C.c_void_p]
         L.dc_quantise_host.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t,
                                        C.c_void_p, C.c_float, C.c_float]
+        L.dc_set_pinhole_f64.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_double] * 4
+        L.dc_set_equirectangular_f64.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double,
+                                                 C.c_double]
+        L.dc_quantise_host_f64.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                           C.c_size_t, C.c_void_p, C.c_double, C.c_double]
         L.dc_kernel_launches.restype = C.c_uint64
         L.dc_kernel_launches.argtypes = [C.c_void_p]
         _lib = L
     return _lib
 
 
-_IN_DTYPE = {DC_IN_U16_DEPTH: np.uint16, DC_IN_U16_RANGE: np.uint16, DC_IN_F32_RANGE: np.float32}
-_OUT_DTYPE = {DC_OUT_F32: np.float32, DC_OUT_U16: np.uint16}
+_IN_DTYPE = {DC_IN_U16_DEPTH: np.uint16, DC_IN_U16_RANGE: np.uint16, DC_IN_F32_RANGE: np.float32,
+             DC_IN_F64_RANGE: np.float64}
+_OUT_DTYPE = {DC_OUT_F32: np.float32, DC_OUT_U16: np.uint16, DC_OUT_F64: np.float64}
 
 
 class Context:
@@ -132,6 +139,12 @@ class Context:
     # -- camera ------------------------------------------------------------
     def set_pinhole(self, w, h, fx, fy, cx, cy):
         self._check(self._L.dc_set_pinhole(self._h, w, h, fx, fy, cx, cy))
+
+    def set_pinhole_f64(self, w, h, fx, fy, cx, cy):
+        self._check(self._L.dc_set_pinhole_f64(self._h, w, h, fx, fy, cx, cy))
+
+    def set_equirectangular_f64(self, w, h, theta_min, theta_max):
+        self._check(self._L.dc_set_equirectangular_f64(self._h, w, h, theta_min, theta_max))
 
     def set_equirectangular(self, w, h, theta_min, theta_max):
         self._check(self._L.dc_set_equirectangular(self._h, w, h, theta_min, theta_max))
@@ -190,7 +203,15 @@ class Context:
         return [(o[0] if single else o) if o is not None else None for o in outs]
 
     def quantise(self, quant, feature, mask=None, clamp=(-20.0, 20.0)):
-        """Stand-alone quantiser of the library API: float image -> u16 image."""
+        """Stand-alone quantiser of the library API: float (or double) image -> u16 image."""
+        if np.asarray(feature).dtype == np.float64:
+            feature = np.ascontiguousarray(feature, np.float64)
+            out = np.empty(feature.shape, np.uint16)
+            m = np.ascontiguousarray(mask, np.float64) if mask is not None else None
+            self._check(self._L.dc_quantise_host_f64(
+                self._h, quant, feature.ctypes.data, m.ctypes.data if m is not None else None,
+                feature.size, out.ctypes.data, clamp[0], clamp[1]))
+            return out
         feature = np.ascontiguousarray(feature, np.float32)
         out = np.empty(feature.shape, np.uint16)
         m = np.ascontiguousarray(mask, np.float32) if mask is not None else None

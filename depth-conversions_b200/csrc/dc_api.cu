@@ -3,6 +3,7 @@
 #include "../../include/depthconv_b200.h"
 #include "dc_kernels.cuh"
 #include "dc_pair_kernels.cuh"
+#include "dc_f64.h"
 #include "dc_tables.h"
 
 #include <algorithm>
@@ -54,6 +55,9 @@ struct dc_ctx {
     dev_table    d_range_factor, d_ray[3], d_cos[4], d_curv[3];
     slot         slots[kSlots];
     uint64_t     launches = 0;
+    // Real = double (dc_f64.h): camera parameters in double, tables on demand
+    dc64::camera cam64;
+    dc64::state* f64 = nullptr;
 };
 
 namespace {
@@ -187,18 +191,29 @@ unsigned tables_needed(int feature, int in_kind) {
     return need;
 }
 
-size_t in_elem_bytes(int in_kind) { return in_kind == DC_IN_F32_RANGE ? 4 : 2; }
-size_t out_elem_bytes(int out_kind) { return out_kind == DC_OUT_F32 ? 4 : 2; }
+size_t in_elem_bytes(int in_kind) {
+    return in_kind == DC_IN_F64_RANGE ? 8 : in_kind == DC_IN_F32_RANGE ? 4 : 2;
+}
+size_t out_elem_bytes(int out_kind) {
+    return out_kind == DC_OUT_F64 ? 8 : out_kind == DC_OUT_F32 ? 4 : 2;
+}
 
 int validate_job(dc_ctx* c, const dc_job* j) {
     if (j == nullptr)
         return fail(c, DC_ERR_INVALID, "job is NULL");
     if (j->feature < DC_RANGE || j->feature > DC_SCALE)
         return fail(c, DC_ERR_INVALID, "unknown feature");
-    if (j->in_kind < DC_IN_U16_DEPTH || j->in_kind > DC_IN_F32_RANGE)
+    if (j->in_kind < DC_IN_U16_DEPTH || j->in_kind > DC_IN_F64_RANGE)
         return fail(c, DC_ERR_INVALID, "unknown in_kind");
-    if (j->out_kind < DC_OUT_F32 || j->out_kind > DC_OUT_U16)
+    if (j->out_kind < DC_OUT_F32 || j->out_kind > DC_OUT_F64)
         return fail(c, DC_ERR_INVALID, "unknown out_kind");
+    // Real = double: double out from u16 or double in; nothing mixed with float
+    if (j->in_kind == DC_IN_F64_RANGE && j->out_kind != DC_OUT_F64)
+        return fail(c, DC_ERR_UNSUPPORTED, "DC_IN_F64_RANGE needs DC_OUT_F64");
+    if (j->out_kind == DC_OUT_F64 && j->in_kind == DC_IN_F32_RANGE)
+        return fail(c, DC_ERR_UNSUPPORTED, "double output from a float range image is not defined");
+    if (j->out_kind == DC_OUT_F64 && j->feature == DC_SCALE)
+        return fail(c, DC_ERR_UNSUPPORTED, "scale is u16 -> u16 (depth_scaling.h:21-31)");
     if (j->n_frames < 0)
         return fail(c, DC_ERR_INVALID, "n_frames < 0");
     if (j->n_frames > 0 && j->in == nullptr)
@@ -425,6 +440,23 @@ int launch_job(dc_ctx* c, const dc_job* j, cudaStream_t s) {
     h = c->tabs.cam.h;
     if (w <= 0 || h <= 0)
         return fail(c, DC_ERR_NO_CAMERA, "frame size unknown: dc_set_pinhole / dc_set_frame_size");
+    if (j->out_kind == DC_OUT_F64) {
+        if (j->feature == DC_SCALE)
+            return fail(c, DC_ERR_UNSUPPORTED, "scale is u16 -> u16");
+        if (c->f64 == nullptr) {
+            c->f64 = dc64::create();
+            dc64::set_camera(c->f64, c->cam64);
+        }
+        double* outs[4];
+        for (int k = 0; k < 4; ++k)
+            outs[k] = static_cast<double*>(j->out[k]);
+        std::string       msg;
+        const cudaError_t e = dc64::convert(c->f64, j->feature, j->in_kind, j->in, j->n_frames, outs,
+                                            s, msg, c->launches);
+        if (e != cudaSuccess)
+            return cuda_fail(c, e, msg.c_str());
+        return DC_OK;
+    }
     int in_kind = j->in_kind;
     if (j->feature != DC_SCALE) {
         // equirectangular: the range conversion is the identity (util.h:57-67)
@@ -573,6 +605,7 @@ void dc_destroy(dc_ctx* c) {
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
     drop_device_tables(c);
+    dc64::destroy(c->f64);
     for (auto& s : c->slots) {
         free_dev(s.d_in);
         free_pinned(s.h_in);
@@ -594,12 +627,19 @@ const char* dc_last_error(const dc_ctx* c) {
     return c != nullptr ? c->err.c_str() : g_create_error.c_str();
 }
 
-static int set_camera(dc_ctx* c, const dc::camera& cam) {
+static int set_camera(dc_ctx* c, const dc::camera& cam, const double* precise = nullptr) {
     DC_CUDA(c, cudaSetDevice(c->device));
     DC_CUDA(c, cudaDeviceSynchronize());
     drop_device_tables(c);
     c->tabs     = dc::tables{};
     c->tabs.cam = cam;
+    c->cam64.model = cam.model == dc::camera_model::pinhole ? 1
+                     : cam.model == dc::camera_model::equirectangular ? 2 : 0;
+    c->cam64.w = cam.w, c->cam64.h = cam.h;
+    for (int k = 0; k < 4; ++k)
+        c->cam64.p[k] = precise != nullptr ? precise[k] : double(cam.p[k]);
+    if (c->f64 != nullptr)
+        dc64::set_camera(c->f64, c->cam64);
     return DC_OK;
 }
 
@@ -649,6 +689,38 @@ int dc_set_frame_size(dc_ctx* c, int w, int h) {
     cam.w     = w;
     cam.h     = h;
     return set_camera(c, cam);
+}
+
+int dc_set_pinhole_f64(dc_ctx* c, int w, int h, double fx, double fy, double cx, double cy) {
+    if (c == nullptr)
+        return DC_ERR_INVALID;
+    if (c->sticky)
+        return DC_ERR_CUDA;
+    if (!(w > 0 && h > 0 && fx > 0. && fy > 0. && cx > 0. && cy > 0.))
+        return fail(c, DC_ERR_INVALID, "pinhole needs w, h > 0 and fx, fy, cx, cy > 0");
+    dc::camera cam;
+    cam.model = dc::camera_model::pinhole;
+    cam.w = w, cam.h = h;
+    cam.p[0] = float(fx), cam.p[1] = float(fy), cam.p[2] = float(cx), cam.p[3] = float(cy);
+    const double precise[4] = {fx, fy, cx, cy};
+    return set_camera(c, cam, precise);
+}
+
+int dc_set_equirectangular_f64(dc_ctx* c, int w, int h, double theta_min, double theta_max) {
+    if (c == nullptr)
+        return DC_ERR_INVALID;
+    if (c->sticky)
+        return DC_ERR_CUDA;
+    if (!(w > 0 && h > 0 && theta_min >= 0. && theta_max <= 3.141592653589793238462 &&
+          theta_min < theta_max))
+        return fail(c, DC_ERR_INVALID,
+                    "equirectangular needs w, h > 0 and 0 <= theta_min < theta_max <= pi");
+    dc::camera cam;
+    cam.model = dc::camera_model::equirectangular;
+    cam.w = w, cam.h = h;
+    cam.p[0] = float(theta_min), cam.p[1] = float(theta_max);
+    const double precise[4] = {theta_min, theta_max, 0., 0.};
+    return set_camera(c, cam, precise);
 }
 
 int dc_width(const dc_ctx* c) { return c != nullptr ? c->tabs.cam.w : 0; }
@@ -788,6 +860,46 @@ int dc_quantise_host(dc_ctx* c, int quant, const float* feature, const float* ma
         quant, static_cast<const float*>(s.d_in.p), static_cast<const float*>(s.d_out[0].p), n_px,
         static_cast<unsigned short*>(s.d_out[1].p), alpha, clamp_lo, clamp_hi);
     const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess)
+        return cuda_fail(c, e, "quantise kernel launch");
+    c->launches += 1;
+    DC_CUDA(c, cudaMemcpyAsync(out, s.d_out[1].p, n_px * sizeof(uint16_t), cudaMemcpyDeviceToHost,
+                               s.stream));
+    DC_CUDA(c, cudaStreamSynchronize(s.stream));
+    return DC_OK;
+}
+
+int dc_quantise_host_f64(dc_ctx* c, int quant, const double* feature, const double* mask,
+                         size_t n_px, uint16_t* out, double clamp_lo, double clamp_hi) {
+    if (c == nullptr)
+        return DC_ERR_INVALID;
+    if (c->sticky)
+        return DC_ERR_CUDA;
+    if (quant < DC_Q_RANGE || quant > DC_Q_MAX_CURVE)
+        return fail(c, DC_ERR_INVALID, "unknown quantiser");
+    if (n_px == 0)
+        return DC_OK;
+    if (feature == nullptr || out == nullptr)
+        return fail(c, DC_ERR_INVALID, "quantiser buffers are NULL");
+    if (quant == DC_Q_CURVATURE && (mask == nullptr || !(clamp_lo < clamp_hi)))
+        return fail(c, DC_ERR_INVALID,
+                    "curvature quantiser needs the range image as mask and lower < upper bound");
+    DC_CUDA(c, cudaSetDevice(c->device));
+    slot& s  = c->slots[0];
+    int   rc = finish_slot(c, s);
+    if (rc != DC_OK)
+        return rc;
+    DC_CUDA(c, reserve_dev(s.d_in, n_px * sizeof(double)));
+    DC_CUDA(c, reserve_dev(s.d_out[0], n_px * sizeof(double)));
+    DC_CUDA(c, reserve_dev(s.d_out[1], n_px * sizeof(uint16_t)));
+    DC_CUDA(c, cudaMemcpyAsync(s.d_in.p, feature, n_px * sizeof(double), cudaMemcpyHostToDevice,
+                               s.stream));
+    if (quant == DC_Q_CURVATURE)
+        DC_CUDA(c, cudaMemcpyAsync(s.d_out[0].p, mask, n_px * sizeof(double),
+                                   cudaMemcpyHostToDevice, s.stream));
+    const cudaError_t e = dc64::quantise(
+        quant, static_cast<const double*>(s.d_in.p), static_cast<const double*>(s.d_out[0].p), n_px,
+        static_cast<uint16_t*>(s.d_out[1].p), clamp_lo, clamp_hi, s.stream);
     if (e != cudaSuccess)
         return cuda_fail(c, e, "quantise kernel launch");
     c->launches += 1;

@@ -1,5 +1,7 @@
 // sens_loc::conversion::* -- the drop-in replacements of the reference's
-// depth -> feature functions for Real = float, same names and argument meaning
+// depth -> feature functions for Real = float (what depth2x instantiates) and
+// Real = double (what the reference's unit tests instantiate,
+// src/unittest/conversion/intrinsic.h:8-26), same names and argument meaning
 // (src/include/sens_loc/conversion/*.h). Every function checks its sizes, hands
 // the pixels to libdepthconv_b200.so (sm_100a kernels) and returns an owning
 // image; nothing is computed on the host.
@@ -38,15 +40,24 @@ inline dc_job job(int feature, int in_kind, int out_kind, const void* in) {
     j.scale = 1., j.offset = 0.;
     return j;
 }
-template <typename Intrinsic>
-inline math::image<float> one_output(int feature, int slot, const math::image<float>& range,
-                                     const Intrinsic& k) {
+template <typename Real>
+struct kinds {
+    static_assert(std::is_same_v<Real, float> || std::is_same_v<Real, double>,
+                  "the B200 path carries Real = float and Real = double");
+    static constexpr int in  = std::is_same_v<Real, float> ? DC_IN_F32_RANGE : DC_IN_F64_RANGE;
+    static constexpr int out = std::is_same_v<Real, float> ? DC_OUT_F32 : DC_OUT_F64;
+};
+template <typename Real, typename Intrinsic>
+inline math::image<Real> one_output(int feature, int slot, const math::image<Real>& range,
+                                    const Intrinsic& k) {
+    static_assert(std::is_same_v<typename Intrinsic::real_type, Real>,
+                  "image and intrinsic must have the same Real");
     expect_same_size(range, k);
     gpu::context& g = gpu::context::mine();
     g.use(k);
-    math::image<float> out(range.w(), range.h());
-    dc_job             j = job(feature, DC_IN_F32_RANGE, DC_OUT_F32, range.data());
-    j.out[slot]          = out.data();
+    math::image<Real> out(range.w(), range.h());
+    dc_job            j = job(feature, kinds<Real>::in, kinds<Real>::out, range.data());
+    j.out[slot]         = out.data();
     g.convert_host(j);
     return out;
 }
@@ -56,13 +67,12 @@ inline math::image<float> one_output(int feature, int slot, const math::image<fl
 template <typename Real = float, typename PixelType = ushort, typename Intrinsic>
 inline math::image<Real> depth_to_laserscan(const math::image<PixelType>& depth_image,
                                             const Intrinsic&              intrinsic) {
-    static_assert(std::is_same_v<Real, float> && std::is_same_v<PixelType, ushort>,
-                  "the B200 path carries Real = float, PixelType = ushort");
+    static_assert(std::is_same_v<PixelType, ushort>, "the B200 path carries PixelType = ushort");
     detail::expect_same_size(depth_image, intrinsic);
     gpu::context& g = gpu::context::mine();
     g.use(intrinsic);
-    math::image<float> out(depth_image.w(), depth_image.h());
-    dc_job j = detail::job(DC_RANGE, DC_IN_U16_DEPTH, DC_OUT_F32, depth_image.data());
+    math::image<Real> out(depth_image.w(), depth_image.h());
+    dc_job j = detail::job(DC_RANGE, DC_IN_U16_DEPTH, detail::kinds<Real>::out, depth_image.data());
     j.out[0] = out.data();
     g.convert_host(j);
     return out;
@@ -72,8 +82,7 @@ inline math::image<Real> depth_to_laserscan(const math::image<PixelType>& depth_
 template <direction Direction, typename Real = float, typename Intrinsic>
 inline math::image<Real> depth_to_bearing(const math::image<Real>& depth_image,
                                           const Intrinsic&         intrinsic) {
-    static_assert(std::is_same_v<Real, float>);
-    return detail::one_output(DC_BEARING, int(Direction), depth_image, intrinsic);
+    return detail::one_output<Real>(DC_BEARING, int(Direction), depth_image, intrinsic);
 }
 /// All requested directions in one pass over the image (the reference makes one
 /// pass per direction, converter_bearing.h.inl:13-26). Slots not wanted stay empty.
@@ -93,34 +102,35 @@ inline void depth_to_bearing_all(const math::image<float>& depth_image, const In
 }
 
 /// depth_to_flexion.h:147-167
-template <typename Intrinsic>
-inline math::image<float> depth_to_flexion(const math::image<float>& depth_image,
-                                           const Intrinsic&          intrinsic) {
-    return detail::one_output(DC_FLEXION, 0, depth_image, intrinsic);
+template <typename Intrinsic, typename Real = typename Intrinsic::real_type>
+inline math::image<Real> depth_to_flexion(const math::image<Real>& depth_image,
+        const Intrinsic& intrinsic) {
+    return detail::one_output<Real>(DC_FLEXION, 0, depth_image, intrinsic);
 }
 /// depth_to_curvature.h:166-184
-template <typename Intrinsic>
-inline math::image<float> depth_to_gaussian_curvature(const math::image<float>& depth_image,
-                                                      const Intrinsic&          intrinsic) {
-    return detail::one_output(DC_CURVATURE, 0, depth_image, intrinsic);
+template <typename Intrinsic, typename Real = typename Intrinsic::real_type>
+inline math::image<Real> depth_to_gaussian_curvature(const math::image<Real>& depth_image,
+        const Intrinsic& intrinsic) {
+    return detail::one_output<Real>(DC_CURVATURE, 0, depth_image, intrinsic);
 }
 /// depth_to_curvature.h:188-206
-template <typename Intrinsic>
-inline math::image<float> depth_to_mean_curvature(const math::image<float>& depth_image,
-                                                  const Intrinsic&          intrinsic) {
-    return detail::one_output(DC_CURVATURE, 1, depth_image, intrinsic);
+template <typename Intrinsic, typename Real = typename Intrinsic::real_type>
+inline math::image<Real> depth_to_mean_curvature(const math::image<Real>& depth_image,
+        const Intrinsic& intrinsic) {
+    return detail::one_output<Real>(DC_CURVATURE, 1, depth_image, intrinsic);
 }
 /// depth_to_max_curve.h:86-153
-template <typename Intrinsic>
-inline math::image<float> depth_to_max_curve(const math::image<float>& depth_image,
-                                             const Intrinsic&          intrinsic) {
-    return detail::one_output(DC_MAX_CURVE, 0, depth_image, intrinsic);
+template <typename Intrinsic, typename Real = typename Intrinsic::real_type>
+inline math::image<Real> depth_to_max_curve(const math::image<Real>& depth_image,
+        const Intrinsic& intrinsic) {
+    return detail::one_output<Real>(DC_MAX_CURVE, 0, depth_image, intrinsic);
 }
 
 // ---- quantisers -----------------------------------------------------------
 namespace detail {
-inline math::image<ushort> quantise(int quant, const math::image<float>& img,
-                                    const math::image<float>* mask, float lo, float hi) {
+template <typename Real>
+inline math::image<ushort> quantise(int quant, const math::image<Real>& img,
+                                    const math::image<Real>* mask, Real lo, Real hi) {
     if (img.empty() || (mask != nullptr && (mask->w() != img.w() || mask->h() != img.h())))
         throw std::invalid_argument("quantiser: empty image or mask of another size");
     math::image<ushort> out(img.w(), img.h());
@@ -133,39 +143,38 @@ inline math::image<ushort> quantise(int quant, const math::image<float>& img,
 /// depth_to_bearing.h:282-301
 template <typename Real = float, typename PixelType = ushort>
 inline math::image<PixelType> convert_bearing(const math::image<Real>& bearing_image) {
-    static_assert(std::is_same_v<Real, float> && std::is_same_v<PixelType, ushort>);
-    return detail::quantise(DC_Q_BEARING, bearing_image, nullptr, 0.f, 0.f);
+    static_assert(std::is_same_v<PixelType, ushort>);
+    return detail::quantise<Real>(DC_Q_BEARING, bearing_image, nullptr, Real(0), Real(0));
 }
 /// depth_to_flexion.h:194-215
 template <typename PixelType = ushort, typename Real = float>
 inline math::image<PixelType> convert_flexion(const math::image<Real>& flexion_image) {
-    static_assert(std::is_same_v<Real, float> && std::is_same_v<PixelType, ushort>);
-    return detail::quantise(DC_Q_FLEXION, flexion_image, nullptr, 0.f, 0.f);
+    static_assert(std::is_same_v<PixelType, ushort>);
+    return detail::quantise<Real>(DC_Q_FLEXION, flexion_image, nullptr, Real(0), Real(0));
 }
 /// depth_to_max_curve.h:156-176
 template <typename PixelType = ushort, typename Real = float>
 inline math::image<PixelType> convert_max_curve(const math::image<Real>& max_curve_image) {
-    static_assert(std::is_same_v<Real, float> && std::is_same_v<PixelType, ushort>);
-    return detail::quantise(DC_Q_MAX_CURVE, max_curve_image, nullptr, 0.f, 0.f);
+    static_assert(std::is_same_v<PixelType, ushort>);
+    return detail::quantise<Real>(DC_Q_MAX_CURVE, max_curve_image, nullptr, Real(0), Real(0));
 }
 /// depth_to_curvature.h:253-283. Both clamps are required here (the tool always
 /// passes them, converter_curvature.h.inl:9-10); the min/max-of-image form is
 /// not provided and throws.
-template <typename PixelType = ushort, typename Real = float, typename MaskType = float>
+template <typename PixelType = ushort, typename Real = float, typename MaskType = Real>
 inline math::image<PixelType> curvature_to_image(const math::image<Real>&     curvature_img,
                                                  const math::image<MaskType>& depth_image_as_mask,
                                                  std::optional<Real> clamp_min = std::nullopt,
                                                  std::optional<Real> clamp_max = std::nullopt) {
-    static_assert(std::is_same_v<Real, float> && std::is_same_v<PixelType, ushort> &&
-                  std::is_same_v<MaskType, float>);
+    static_assert(std::is_same_v<PixelType, ushort> && std::is_same_v<MaskType, Real>);
     if (!clamp_min || !clamp_max)
         throw std::invalid_argument("curvature_to_image: both clamps are required on the B200 path");
-    return detail::quantise(DC_Q_CURVATURE, curvature_img, &depth_image_as_mask, *clamp_min,
-                            *clamp_max);
+    return detail::quantise<Real>(DC_Q_CURVATURE, curvature_img, &depth_image_as_mask, *clamp_min,
+                                  *clamp_max);
 }
 /// range image -> 16 bit, apps/depth2x/converter_laserscan.h.inl:9-10
 inline math::image<ushort> convert_range(const math::image<float>& range_image) {
-    return detail::quantise(DC_Q_RANGE, range_image, nullptr, 0.f, 0.f);
+    return detail::quantise<float>(DC_Q_RANGE, range_image, nullptr, 0.f, 0.f);
 }
 
 /// depth_scaling.h:21-31: saturate(round(depth * scale + offset))

@@ -59,14 +59,29 @@ class context {
         }
     }
     void use(const camera_models::equirectangular<float>& k) {
-        const key want{2, k.w(), k.h(), {k.theta_min(), k.theta_max(), 0.f, 0.f}};
+        const key want{2, k.w(), k.h(), {k.theta_min(), k.theta_max(), 0., 0.}};
         if (!(want == _cam)) {
             check(dc_set_equirectangular(_c, k.w(), k.h(), k.theta_min(), k.theta_max()));
             _cam = want;
         }
     }
+    // Real = double cameras: kept in double on the library side (dc_set_*_f64)
+    void use(const camera_models::pinhole<double>& k) {
+        const key want{3, k.w(), k.h(), {k.fx(), k.fy(), k.cx(), k.cy()}};
+        if (!(want == _cam)) {
+            check(dc_set_pinhole_f64(_c, k.w(), k.h(), k.fx(), k.fy(), k.cx(), k.cy()));
+            _cam = want;
+        }
+    }
+    void use(const camera_models::equirectangular<double>& k) {
+        const key want{4, k.w(), k.h(), {k.theta_min(), k.theta_max(), 0., 0.}};
+        if (!(want == _cam)) {
+            check(dc_set_equirectangular_f64(_c, k.w(), k.h(), k.theta_min(), k.theta_max()));
+            _cam = want;
+        }
+    }
     void use_frame_size(int w, int h) {
-        const key want{0, w, h, {0.f, 0.f, 0.f, 0.f}};
+        const key want{0, w, h, {0., 0., 0., 0.}};
         if (!(want == _cam)) {
             check(dc_set_frame_size(_c, w, h));
             _cam = want;
@@ -80,13 +95,17 @@ class context {
                   std::uint16_t* out, float lo, float hi) {
         check(dc_quantise_host(_c, quant, feature, mask, n, out, lo, hi));
     }
+    void quantise(int quant, const double* feature, const double* mask, std::size_t n,
+                  std::uint16_t* out, double lo, double hi) {
+        check(dc_quantise_host_f64(_c, quant, feature, mask, n, out, lo, hi));
+    }
     [[nodiscard]] const char* last_error() const noexcept { return dc_last_error(_c); }
     [[nodiscard]] dc_ctx*     raw() noexcept { return _c; }
 
   private:
     struct key {
-        int   model = -1, w = 0, h = 0;
-        float p[4] = {0, 0, 0, 0};
+        int    model = -1, w = 0, h = 0;
+        double p[4] = {0, 0, 0, 0};
         bool  operator==(const key& o) const {
             return model == o.model && w == o.w && h == o.h && p[0] == o.p[0] && p[1] == o.p[1] &&
                    p[2] == o.p[2] && p[3] == o.p[3];

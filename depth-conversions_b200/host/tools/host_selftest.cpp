@@ -40,6 +40,14 @@ static bool save_f32(const std::string& path, const math::image<float>& img) {
     return std::fclose(f) == 0 && ok;
 }
 
+static bool save_f64(const std::string& path, const math::image<double>& img) {
+    std::FILE* f = std::fopen(path.c_str(), "wb");
+    if (f == nullptr)
+        return false;
+    const bool ok = std::fwrite(img.data(), sizeof(double), img.pixels(), f) == img.pixels();
+    return std::fclose(f) == 0 && ok;
+}
+
 int main(int argc, char** argv) try {
     const std::string cmd = argc > 1 ? argv[1] : "";
     if (cmd == "png" && argc == 4) {
@@ -91,6 +99,35 @@ int main(int argc, char** argv) try {
             threw = true;
         }
         return ok && threw ? 0 : 4;
+    }
+    if (cmd == "api64" && argc == 5) {
+        // the Real = double instantiations, as src/unittest/conversion/*.cpp call them
+        std::ifstream in{argv[2]};
+        const auto    k = io::camera<double, camera_models::pinhole>::load_intrinsic(in);
+        if (!k)
+            return 2;
+        math::image<ushort> depth;
+        if (!load_u16(argv[3], depth))
+            return 3;
+        const std::string dir = std::string(argv[4]) + "/";
+        using namespace conversion;
+        const math::image<double> range = depth_to_laserscan<double, ushort>(depth, *k);
+        bool ok = save_f64(dir + "range.f64", range);
+        const auto bh = depth_to_bearing<direction::horizontal, double>(range, *k);
+        const auto ba = depth_to_bearing<direction::antidiagonal, double>(range, *k);
+        ok = ok && save_f64(dir + "bearing_h.f64", bh) && save_f64(dir + "bearing_a.f64", ba) &&
+             save_u16(dir + "bearing_h64.png", convert_bearing<double, ushort>(bh));
+        const auto fl = depth_to_flexion(range, *k);
+        ok = ok && save_f64(dir + "flexion.f64", fl) &&
+             save_u16(dir + "flexion64.png", convert_flexion<ushort, double>(fl));
+        const auto g = depth_to_gaussian_curvature(range, *k);
+        const auto m = depth_to_mean_curvature(range, *k);
+        ok = ok && save_f64(dir + "gauss.f64", g) && save_f64(dir + "mean.f64", m) &&
+             save_u16(dir + "gauss64.png", curvature_to_image<ushort, double>(g, range, {-20.}, {20.}));
+        const auto mc = depth_to_max_curve(range, *k);
+        ok = ok && save_f64(dir + "max_curve.f64", mc) &&
+             save_u16(dir + "max_curve64.png", convert_max_curve<ushort, double>(mc));
+        return ok ? 0 : 4;
     }
     std::cerr << "usage: host_selftest png <in.png> <out.png> | api <intrinsic> <depth.png> <outdir>\n";
     return 64;

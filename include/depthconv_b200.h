@@ -88,19 +88,27 @@ typedef enum dc_in_kind {
                             range first (batch_converter.h:157-159) */
     DC_IN_U16_RANGE = 1, /* --type pinhole-range: Euclidean u16, widened to
                             float (batch_converter.h:160) */
-    DC_IN_F32_RANGE = 2  /* math::image<float> range image: the argument type of
+    DC_IN_F32_RANGE = 2, /* math::image<float> range image: the argument type of
                             the conversion::depth_to_* library functions */
+    DC_IN_F64_RANGE = 3  /* math::image<double> range image: the Real = double
+                            instantiation (src/unittest/conversion/intrinsic.h:8-26);
+                            requires DC_OUT_F64 */
 } dc_in_kind;
 
 /* What the output pixels are. */
 typedef enum dc_out_kind {
     DC_OUT_F32 = 0, /* the float feature image the library functions return */
-    DC_OUT_U16 = 1  /* the 16 bit image depth2x writes: convert_bearing<float,
+    DC_OUT_U16 = 1, /* the 16 bit image depth2x writes: convert_bearing<float,
                        ushort> (depth_to_bearing.h:282-301), convert_flexion
                        <ushort> (depth_to_flexion.h:194-215), convert_max_curve
                        <ushort> (depth_to_max_curve.h:156-176), curvature_to_image
                        <ushort> with both clamps (depth_to_curvature.h:253-283),
                        convertTo(CV_16U) for range (converter_laserscan.h.inl:9-10) */
+    DC_OUT_F64 = 2  /* Real = double: every operation of the path in double, as the
+                       reference's templates instantiated with double compute it
+                       (camera from dc_set_*_f64, or the float parameters widened).
+                       Input DC_IN_U16_DEPTH / DC_IN_U16_RANGE / DC_IN_F64_RANGE.
+                       Not for DC_SCALE. */
 } dc_out_kind;
 
 #define DC_MAX_OUTPUTS 4
@@ -148,6 +156,12 @@ int dc_set_pinhole(dc_ctx* ctx, int w, int h, float fx, float fy, float cx, floa
  * identity (conversion/util.h:57-67). */
 int dc_set_equirectangular(dc_ctx* ctx, int w, int h, float theta_min, float theta_max);
 
+/* The same two constructors for Real = double (camera_models::pinhole<double>,
+ * equirectangular<double>): the parameters are kept in double for DC_OUT_F64
+ * jobs; float jobs on this context see them narrowed to float. */
+int dc_set_pinhole_f64(dc_ctx* ctx, int w, int h, double fx, double fy, double cx, double cy);
+int dc_set_equirectangular_f64(dc_ctx* ctx, int w, int h, double theta_min, double theta_max);
+
 /* Frame size only, no camera model: all that DC_SCALE needs (`depth2x scale`
  * takes no --calibration; apps/depth2x/main.cpp:338-352). Clears any camera. */
 int dc_set_frame_size(dc_ctx* ctx, int w, int h);
@@ -191,6 +205,10 @@ typedef enum dc_quant {
  * provided: pass both clamps. */
 int dc_quantise_host(dc_ctx* ctx, int quant, const float* feature, const float* mask,
                      size_t n_px, uint16_t* out, float clamp_lo, float clamp_hi);
+
+/* The same for Real = double images (convert_bearing<double, ushort> etc.). */
+int dc_quantise_host_f64(dc_ctx* ctx, int quant, const double* feature, const double* mask,
+                         size_t n_px, uint16_t* out, double clamp_lo, double clamp_hi);
 
 /* Block until all work this context enqueued on its own streams has finished. */
 int dc_synchronize(dc_ctx* ctx);
