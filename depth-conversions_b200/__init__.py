@@ -31,7 +31,7 @@ EXPORTED_SYMBOLS = [
     "dc_height", "dc_convert_device", "dc_convert_host", "dc_synchronize",
     "dc_host_alloc", "dc_host_free", "dc_synth_depth_device", "dc_kernel_launches",
     "dc_quantise_host", "dc_set_pinhole_f64", "dc_set_equirectangular_f64",
-    "dc_quantise_host_f64",
+    "dc_quantise_host_f64", "dc_median_host", "dc_median_device",
 ]
 DC_Q_RANGE, DC_Q_BEARING, DC_Q_FLEXION, DC_Q_CURVATURE, DC_Q_MAX_CURVE = range(5)
 
@@ -41,7 +41,7 @@ class DcJob(C.Structure):
         ("feature", C.c_int32), ("in_kind", C.c_int32), ("out_kind", C.c_int32),
         ("n_frames", C.c_int32), ("in_", C.c_void_p), ("out", C.c_void_p * 4),
         ("clamp_lo", C.c_float), ("clamp_hi", C.c_float),
-        ("scale", C.c_double), ("offset", C.c_double),
+        ("scale", C.c_double), ("offset", C.c_double), ("median_ksize", C.c_int32),
     ]
 
 
@@ -90,6 +90,9 @@ def lib():
                                                  C.c_double]
         L.dc_quantise_host_f64.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                            C.c_size_t, C.c_void_p, C.c_double, C.c_double]
+        L.dc_median_host.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.dc_median_device.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int,
+                                       C.c_void_p, C.c_void_p]
         L.dc_kernel_launches.restype = C.c_uint64
         L.dc_kernel_launches.argtypes = [C.c_void_p]
         _lib = L
@@ -165,7 +168,7 @@ class Context:
 
     # -- raw calls -----------------------------------------------------------
     def make_job(self, feature, in_kind, out_kind, n_frames, in_ptr, out_ptrs,
-                 clamp=(-20.0, 20.0), scale=1.0, offset=0.0):
+                 clamp=(-20.0, 20.0), scale=1.0, offset=0.0, median=0):
         j = DcJob()
         j.feature, j.in_kind, j.out_kind, j.n_frames = feature, in_kind, out_kind, n_frames
         j.in_ = in_ptr
@@ -173,6 +176,7 @@ class Context:
             j.out[k] = out_ptrs[k] if k < len(out_ptrs) and out_ptrs[k] else None
         j.clamp_lo, j.clamp_hi = clamp
         j.scale, j.offset = scale, offset
+        j.median_ksize = median
         return j
 
     def convert_device_raw(self, job, stream=None):
@@ -186,7 +190,7 @@ class Context:
 
     # -- numpy convenience (host buffers) -----------------------------------
     def convert(self, feature, frames, in_kind, out_kind=DC_OUT_F32, want=(True,),
-                clamp=(-20.0, 20.0), scale=1.0, offset=0.0):
+                clamp=(-20.0, 20.0), scale=1.0, offset=0.0, median=0):
         """frames: (n, h, w) or (h, w) array of the in_kind dtype. `want[k]`
         selects output slot k. Returns a list with an array (same leading shape)
         per wanted slot, None for the others."""
@@ -198,9 +202,19 @@ class Context:
                 for k in range(4)]
         job = self.make_job(feature, in_kind, out_kind, n, f3.ctypes.data,
                             [o.ctypes.data if o is not None else None for o in outs],
-                            clamp, scale, offset)
+                            clamp, scale, offset, median)
         self._check(self.convert_host_raw(job))
         return [(o[0] if single else o) if o is not None else None for o in outs]
+
+    def median(self, frames, ksize):
+        """preprocess::median_blur on (n, h, w) or (h, w) uint16 / float32 frames."""
+        frames = np.ascontiguousarray(frames)
+        kind = {np.dtype(np.uint16): DC_IN_U16_RANGE, np.dtype(np.float32): DC_IN_F32_RANGE}[frames.dtype]
+        n = 1 if frames.ndim == 2 else frames.shape[0]
+        out = np.empty_like(frames)
+        self._check(self._L.dc_median_host(self._h, kind, frames.ctypes.data, n, ksize,
+                                           out.ctypes.data))
+        return out
 
     def quantise(self, quant, feature, mask=None, clamp=(-20.0, 20.0)):
         """Stand-alone quantiser of the library API: float (or double) image -> u16 image."""

@@ -2,6 +2,7 @@
 // dispatch and the host-buffer pipeline. See include/depthconv_b200.h.
 #include "../../include/depthconv_b200.h"
 #include "dc_kernels.cuh"
+#include "dc_median.cuh"
 #include "dc_pair_kernels.cuh"
 #include "dc_f64.h"
 #include "dc_tables.h"
@@ -11,6 +12,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -58,6 +60,9 @@ struct dc_ctx {
     // Real = double (dc_f64.h): camera parameters in double, tables on demand
     dc64::camera cam64;
     dc64::state* f64 = nullptr;
+    // filtered copy of the input frames (dc_job::median_ksize), one per stream:
+    // the chunks of dc_convert_host run concurrently on the slots' streams
+    std::map<cudaStream_t, dev_buf> d_median;
 };
 
 namespace {
@@ -214,6 +219,12 @@ int validate_job(dc_ctx* c, const dc_job* j) {
         return fail(c, DC_ERR_UNSUPPORTED, "double output from a float range image is not defined");
     if (j->out_kind == DC_OUT_F64 && j->feature == DC_SCALE)
         return fail(c, DC_ERR_UNSUPPORTED, "scale is u16 -> u16 (depth_scaling.h:21-31)");
+    if (j->median_ksize != 0) {
+        if (j->median_ksize != 3 && j->median_ksize != 5)
+            return fail(c, DC_ERR_INVALID, "median_ksize must be 0, 3 or 5 (filter_functor.h:57-60)");
+        if (j->in_kind != DC_IN_U16_DEPTH && j->in_kind != DC_IN_U16_RANGE)
+            return fail(c, DC_ERR_UNSUPPORTED, "the fused median pre-filter takes u16 input frames");
+    }
     if (j->n_frames < 0)
         return fail(c, DC_ERR_INVALID, "n_frames < 0");
     if (j->n_frames > 0 && j->in == nullptr)
@@ -440,6 +451,26 @@ int launch_job(dc_ctx* c, const dc_job* j, cudaStream_t s) {
     h = c->tabs.cam.h;
     if (w <= 0 || h <= 0)
         return fail(c, DC_ERR_NO_CAMERA, "frame size unknown: dc_set_pinhole / dc_set_frame_size");
+    dc_job filtered;
+    if (j->median_ksize != 0) {
+        const size_t bytes = size_t(j->n_frames) * size_t(w) * h * sizeof(uint16_t);
+        dev_buf&     tmp   = c->d_median[s];
+        if (tmp.cap < bytes) {
+            // (a growing buffer is freed only after everything that reads it ran)
+            DC_CUDA(c, cudaStreamSynchronize(s));
+            DC_CUDA(c, reserve_dev(tmp, bytes));
+        }
+        const cudaError_t e = dc::med::launch_median(
+            static_cast<const unsigned short*>(j->in), static_cast<unsigned short*>(tmp.p), w, h,
+            j->n_frames, j->median_ksize, s);
+        if (e != cudaSuccess)
+            return cuda_fail(c, e, "median kernel launch");
+        c->launches += uint64_t((j->n_frames + 65534) / 65535);
+        filtered              = *j;
+        filtered.in           = tmp.p;
+        filtered.median_ksize = 0;
+        j                     = &filtered;
+    }
     if (j->out_kind == DC_OUT_F64) {
         if (j->feature == DC_SCALE)
             return fail(c, DC_ERR_UNSUPPORTED, "scale is u16 -> u16");
@@ -606,6 +637,8 @@ void dc_destroy(dc_ctx* c) {
     cudaDeviceSynchronize();
     drop_device_tables(c);
     dc64::destroy(c->f64);
+    for (auto& kv : c->d_median)
+        free_dev(kv.second);
     for (auto& s : c->slots) {
         free_dev(s.d_in);
         free_pinned(s.h_in);
@@ -906,6 +939,70 @@ int dc_quantise_host_f64(dc_ctx* c, int quant, const double* feature, const doub
     DC_CUDA(c, cudaMemcpyAsync(out, s.d_out[1].p, n_px * sizeof(uint16_t), cudaMemcpyDeviceToHost,
                                s.stream));
     DC_CUDA(c, cudaStreamSynchronize(s.stream));
+    return DC_OK;
+}
+
+static int median_check(dc_ctx* c, int elem_kind, const void* in, int n_frames, int ksize,
+                        const void* out) {
+    if (c == nullptr)
+        return DC_ERR_INVALID;
+    if (c->sticky)
+        return DC_ERR_CUDA;
+    if (elem_kind != DC_IN_U16_RANGE && elem_kind != DC_IN_F32_RANGE)
+        return fail(c, DC_ERR_INVALID, "median: elem_kind is DC_IN_U16_RANGE or DC_IN_F32_RANGE");
+    if (ksize != 3 && ksize != 5)
+        return fail(c, DC_ERR_INVALID, "median: ksize must be 3 or 5 (filter_functor.h:57-60)");
+    if (n_frames < 0 || (n_frames > 0 && (in == nullptr || out == nullptr)) || in == out)
+        return fail(c, DC_ERR_INVALID, "median: bad buffers");
+    if (c->tabs.cam.w <= 0 || c->tabs.cam.h <= 0)
+        return fail(c, DC_ERR_NO_CAMERA, "frame size unknown: dc_set_frame_size");
+    return DC_OK;
+}
+
+int dc_median_device(dc_ctx* c, int elem_kind, const void* in, int n_frames, int ksize, void* out,
+                     void* cuda_stream) {
+    const int rc = median_check(c, elem_kind, in, n_frames, ksize, out);
+    if (rc != DC_OK || n_frames == 0)
+        return rc;
+    DC_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = cuda_stream != nullptr ? static_cast<cudaStream_t>(cuda_stream) : c->stream;
+    const int    w = c->tabs.cam.w, h = c->tabs.cam.h;
+    const cudaError_t e =
+        elem_kind == DC_IN_U16_RANGE
+            ? dc::med::launch_median(static_cast<const unsigned short*>(in),
+                                     static_cast<unsigned short*>(out), w, h, n_frames, ksize, s)
+            : dc::med::launch_median(static_cast<const float*>(in), static_cast<float*>(out), w, h,
+                                     n_frames, ksize, s);
+    if (e != cudaSuccess)
+        return cuda_fail(c, e, "median kernel launch");
+    c->launches += uint64_t((n_frames + 65534) / 65535);
+    return DC_OK;
+}
+
+int dc_median_host(dc_ctx* c, int elem_kind, const void* in, int n_frames, int ksize, void* out) {
+    int rc = median_check(c, elem_kind, in, n_frames, ksize, out);
+    if (rc != DC_OK || n_frames == 0)
+        return rc;
+    DC_CUDA(c, cudaSetDevice(c->device));
+    const size_t fb = size_t(c->tabs.cam.w) * c->tabs.cam.h * (elem_kind == DC_IN_U16_RANGE ? 2 : 4);
+    const int chunk = int(std::max<size_t>(1, std::min<size_t>(size_t(n_frames), kChunkTargetBytes / (2 * fb))));
+    slot&     s     = c->slots[0];
+    for (int f0 = 0; f0 < n_frames; f0 += chunk) {
+        const int nf = std::min(chunk, n_frames - f0);
+        rc           = finish_slot(c, s);
+        if (rc != DC_OK)
+            return rc;
+        DC_CUDA(c, reserve_dev(s.d_in, size_t(chunk) * fb));
+        DC_CUDA(c, reserve_dev(s.d_out[0], size_t(chunk) * fb));
+        DC_CUDA(c, cudaMemcpyAsync(s.d_in.p, static_cast<const char*>(in) + size_t(f0) * fb,
+                                   size_t(nf) * fb, cudaMemcpyHostToDevice, s.stream));
+        rc = dc_median_device(c, elem_kind, s.d_in.p, nf, ksize, s.d_out[0].p, s.stream);
+        if (rc != DC_OK)
+            return rc;
+        DC_CUDA(c, cudaMemcpyAsync(static_cast<char*>(out) + size_t(f0) * fb, s.d_out[0].p,
+                                   size_t(nf) * fb, cudaMemcpyDeviceToHost, s.stream));
+        DC_CUDA(c, cudaStreamSynchronize(s.stream));
+    }
     return DC_OK;
 }
 

@@ -123,6 +123,7 @@ parse_result parse_command_line(int argc, char** argv, options& opt, int& exit_c
         {"", "--devices", "Number of GPUs the index range is sharded over (default 1)", K::int_v, &opt.devices, false, nullptr, false},
         {"", "--batch-size", "Frames per GPU batch (default: automatic)", K::int_v, &opt.batch_size, false, nullptr, false},
         {"", "--threads", "PNG codec threads (default: all host cores)", K::int_v, &opt.threads, false, nullptr, false},
+        {"", "--median-blur", "Median pre-filter of the depth image, window 3 or 5 (depth_filter median-blur -d K)", K::int_v, &opt.median, false, nullptr, false},
     };
     auto out_opt = [&](const char* help) {
         return opt_def{"-o", "--output", help, K::string_v, &opt.files.output, true, nullptr, false};

@@ -29,6 +29,7 @@ struct options {
     int devices    = 1;   // --devices N: shard the index range over N GPUs
     int batch_size = 0;   // --batch-size N: frames per GPU batch (0 = automatic)
     int threads    = 0;   // --threads N: PNG codec threads (0 = all host cores)
+    int median     = 0;   // --median-blur K: depth_filter's median (K = 3, 5) fused in front
 };
 
 enum class parse_result { run, exit_ok, exit_error };

@@ -93,6 +93,9 @@ int run(int argc, char** argv) {
         spec.offset    = opt.scale_delta;
     }
 
+    if (opt.median != 0 && opt.median != 3 && opt.median != 5)
+        throw std::invalid_argument{"--median-blur takes 3 or 5"};
+    spec.median = opt.median;
     profile_mark("run_batch begin");
     const run_stats r =
         run_batch(spec, opt.start_idx, opt.end_idx, opt.devices, opt.batch_size, opt.threads);

@@ -342,6 +342,7 @@ void run_device(const convert_spec& spec, int device, int first, int last, int b
                             j.out[s] = b->out[o++].p;
                     j.clamp_lo = spec.clamp_lo, j.clamp_hi = spec.clamp_hi;
                     j.scale = spec.scale, j.offset = spec.offset;
+                    j.median_ksize = spec.median;
                     prof("camera set", j.n_frames);
                     rc = dc_convert_host(ctx, &j);
                     prof("converted", j.n_frames);

@@ -34,6 +34,7 @@ struct convert_spec {
     std::string output[4];     // output pattern per dc_job out[] slot ("" = not wanted)
     float       clamp_lo = -20.f, clamp_hi = 20.f;
     double      scale = 1., offset = 0.;
+    int         median = 0;  // 0, 3, 5: dc_job::median_ksize
     camera_spec camera;
 };
 

@@ -9,6 +9,7 @@
 #include "../sens_loc/conversion/depth_to_bearing.h"
 #include "../sens_loc/io/intrinsics.h"
 #include "../sens_loc/io/png.h"
+#include "../sens_loc/preprocess/filter.h"
 
 #include <cstdio>
 #include <fstream>
@@ -90,7 +91,9 @@ int main(int argc, char** argv) try {
         const auto mc = depth_to_max_curve(range, *k);
         ok = ok && save_f32(dir + "max_curve.f32", mc) &&
              save_u16(dir + "max_curve.png", convert_max_curve<ushort>(mc)) &&
-             save_u16(dir + "scaled.png", depth_scaling(depth, 8., 3.));
+             save_u16(dir + "scaled.png", depth_scaling(depth, 8., 3.)) &&
+             save_u16(dir + "median5.png", preprocess::median_blur(depth, 5)) &&
+             save_f32(dir + "median3.f32", preprocess::median_blur(range, 3));
         // preconditions: a size mismatch is rejected, not computed
         bool threw = false;
         try {

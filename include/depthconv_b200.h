@@ -124,6 +124,12 @@ typedef struct dc_job {
     float       clamp_hi; /* curvature, DC_OUT_U16: --upper-bound (default +20) */
     double      scale;    /* DC_SCALE: --factor */
     double      offset;   /* DC_SCALE: --delta */
+    int32_t     median_ksize; /* 0 = none; 3 or 5: preprocess::median_blur
+                                 (preprocess/filter.h:143-157) applied to the u16
+                                 input frames on the device before the conversion
+                                 (what `depth_filter median-blur -d K` followed by
+                                 depth2x does, scripts/analysis/transformation_step.py:80-96,
+                                 without the PNG round trip). u16 input kinds only. */
 } dc_job;
 
 /* Library / device discovery. */
@@ -209,6 +215,15 @@ int dc_quantise_host(dc_ctx* ctx, int quant, const float* feature, const float* 
 /* The same for Real = double images (convert_bearing<double, ushort> etc.). */
 int dc_quantise_host_f64(dc_ctx* ctx, int quant, const double* feature, const double* mask,
                          size_t n_px, uint16_t* out, double clamp_lo, double clamp_hi);
+
+/* preprocess::median_blur<PixelType>(image, ksize) = cv::medianBlur, ksize 3 or 5,
+ *   include/sens_loc/preprocess/filter.h:143-157 (apps/depth_filter `median-blur`)
+ * on n_frames frames of the installed frame size. elem_kind: DC_IN_U16_RANGE
+ * (u16 pixels) or DC_IN_F32_RANGE (float pixels); `out` has the type of `in`
+ * and must not alias it. HOST buffers, synchronous / DEVICE buffers, enqueued. */
+int dc_median_host(dc_ctx* ctx, int elem_kind, const void* in, int n_frames, int ksize, void* out);
+int dc_median_device(dc_ctx* ctx, int elem_kind, const void* in, int n_frames, int ksize,
+                     void* out, void* cuda_stream);
 
 /* Block until all work this context enqueued on its own streams has finished. */
 int dc_synchronize(dc_ctx* ctx);

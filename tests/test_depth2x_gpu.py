@@ -194,3 +194,7 @@ def test_cpp_library_api(tmp_path, oracle):
         assert_u16_parity(n, got, oracle.quantise(f, f32(n), rng), exact=False)
     assert np.array_equal(cv2.imread(str(tmp_path / "scaled.png"), cv2.IMREAD_UNCHANGED),
                           oracle.depth_scaling(depth, 8.0, 3.0))
+    # preprocess::median_blur (preprocess/filter.h:143-157) == cv::medianBlur
+    assert np.array_equal(cv2.imread(str(tmp_path / "median5.png"), cv2.IMREAD_UNCHANGED),
+                          cv2.medianBlur(depth, 5))
+    assert np.array_equal(f32("median3"), cv2.medianBlur(f32("range"), 3))
