@@ -302,7 +302,7 @@ def run_ours(args, wl):
     value = world * args.steps * F * px / (total_ms * 1e-3) / 1e6
 
     # --- e2e: host buffers through dc_convert_host ---------------------------
-    Fe = args.e2e_frames or min(F, 128)
+    Fe = min(args.e2e_frames or 128, F)
     h_in = torch.empty((Fe, h, w), dtype=torch.uint16).pin_memory()
     h_in.copy_(d_in[:Fe].cpu())
     h_out = [torch.empty((Fe, h, w), dtype=out_dtype).pin_memory() for _ in range(n_out)]

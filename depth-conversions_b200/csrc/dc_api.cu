@@ -23,7 +23,13 @@ namespace {
 thread_local std::string g_create_error;
 
 constexpr int    kSlots            = 3;
-constexpr size_t kChunkTargetBytes = size_t(48) << 20;  // in + out bytes per chunk
+constexpr size_t kChunkDefaultBytes = size_t(48) << 20;  // in + out bytes per chunk
+// (tuning knob: DC_CHUNK_MB in the environment, read once)
+const size_t kChunkTargetBytes = [] {
+    const char* e = std::getenv("DC_CHUNK_MB");
+    const long  n = e != nullptr ? std::atol(e) : 0;
+    return n > 0 ? size_t(n) << 20 : kChunkDefaultBytes;
+}();
 
 struct dev_buf {
     void*  p   = nullptr;
