@@ -323,7 +323,6 @@ cudaError_t launch_pair(const dc::kparams& p, int n_frames, cudaStream_t s) {
     if (blocks > 0x7fffffffLL)
         return cudaErrorInvalidConfiguration;
     const dim3   grid{unsigned(blocks)}, block{unsigned(dc::pr::kPairThreads)};
-    const size_t smem = dc::pr::pair_smem_bytes<FEAT>();
     static const int forced = [] {
         const char* e = std::getenv("DC_PAIR_SPEC");  // debugging: 0 forces the generic kernel
         return e != nullptr ? std::atoi(e) : -1;
@@ -331,13 +330,16 @@ cudaError_t launch_pair(const dc::kparams& p, int n_frames, cudaStream_t s) {
     const int spec = forced == 0 ? 0 : pair_spec<FEAT, IN>(p);
     switch (spec) {
     case dc::pr::SPEC_TABLES:
-        dc::pr::pair_kernel<FEAT, IN, OUT, dc::pr::SPEC_TABLES><<<grid, block, smem, s>>>(p, n_frames, rps);
+        dc::pr::pair_kernel<FEAT, IN, OUT, dc::pr::SPEC_TABLES>
+            <<<grid, block, dc::pr::pair_smem_bytes<FEAT, dc::pr::SPEC_TABLES>(), s>>>(p, n_frames, rps);
         break;
     case dc::pr::SPEC_UNIFORM:
-        dc::pr::pair_kernel<FEAT, IN, OUT, dc::pr::SPEC_UNIFORM><<<grid, block, smem, s>>>(p, n_frames, rps);
+        dc::pr::pair_kernel<FEAT, IN, OUT, dc::pr::SPEC_UNIFORM>
+            <<<grid, block, dc::pr::pair_smem_bytes<FEAT, dc::pr::SPEC_UNIFORM>(), s>>>(p, n_frames, rps);
         break;
     default:
-        dc::pr::pair_kernel<FEAT, IN, OUT, dc::pr::SPEC_GENERIC><<<grid, block, smem, s>>>(p, n_frames, rps);
+        dc::pr::pair_kernel<FEAT, IN, OUT, dc::pr::SPEC_GENERIC>
+            <<<grid, block, dc::pr::pair_smem_bytes<FEAT, dc::pr::SPEC_GENERIC>(), s>>>(p, n_frames, rps);
     }
     return cudaGetLastError();
 }
@@ -356,7 +358,7 @@ cudaError_t launch_flexion_pair(const dc::kparams& p, int n_frames, cudaStream_t
         int(cudaSharedmemCarveoutMaxShared));
     if (carve != cudaSuccess)
         return carve;
-    const size_t smem = size_t(2) * dc::pr::kFlexSlots * dc::pr::kPairThreads * sizeof(uint4);
+    const size_t smem = size_t(3) * dc::pr::kFlexSlots * dc::pr::kPairThreads * sizeof(uint4);
     dc::pr::flexion_pair_kernel<IN, OUT>
         <<<unsigned(blocks), dc::pr::kPairThreads, smem, s>>>(p, n_frames, rps);
     return cudaGetLastError();

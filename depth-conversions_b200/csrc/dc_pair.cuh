@@ -140,6 +140,8 @@ __device__ __forceinline__ void cp_async(void* smem_dst, const void* gsrc, bool 
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+// all groups but the most recently committed one are complete
+__device__ __forceinline__ void cp_async_wait_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 
 // SPEC: what the launch code has already established about a job, so that the
 // row loop carries no pointer tests. At run time those tests cost ~60

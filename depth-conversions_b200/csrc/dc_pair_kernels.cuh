@@ -334,22 +334,32 @@ __device__ __forceinline__ void curvature_row(const kparams& p, const wrow<FEAT_
 }
 
 // ---------------------------------------------------------------------------
-template <int FEAT>
+#ifndef DC_MC_UNIFORM_BLOCKS
+#define DC_MC_UNIFORM_BLOCKS 4
+#endif
+template <int FEAT, int SPEC = SPEC_GENERIC>
 constexpr int min_blocks() {
 #ifdef DC_MIN_BLOCKS
     return DC_MIN_BLOCKS;
 #else
+    if (FEAT == FEAT_MAX_CURVE && SPEC == SPEC_UNIFORM)
+        return DC_MC_UNIFORM_BLOCKS;
     return FEAT == FEAT_CURVATURE ? 3 : 4;  // curvature wants 168 registers (no spills)
 #endif
 }
 
-template <int FEAT>
+// staging slots per stage: SPEC_UNIFORM reads no table
+template <int FEAT, int SPEC>
+__host__ __device__ constexpr int stage_slots() {
+    return kRawSlots + (SPEC == SPEC_UNIFORM ? 0 : tab_slots<FEAT>::n);
+}
+template <int FEAT, int SPEC>
 constexpr size_t pair_smem_bytes() {
-    return size_t(2) * (kRawSlots + tab_slots<FEAT>::n) * kPairThreads * sizeof(uint4);
+    return size_t(2) * stage_slots<FEAT, SPEC>() * kPairThreads * sizeof(uint4);
 }
 
 template <int FEAT, int IN, int OUT, int SPEC>
-__global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT>())
+__global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
     pair_kernel(const __grid_constant__ kparams p, int n_frames, int rows_per_strip) {
     const int       groups_x = p.w >> 2;
     const int       strips   = (p.h + rows_per_strip - 1) / rows_per_strip;
@@ -388,7 +398,7 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT>())
 
     // ---- staging slots of this thread (dc_pair.cuh "Staging") ----
     extern __shared__ uint4 smem[];
-    constexpr int NSLOT = kRawSlots + tab_slots<FEAT>::n;
+    constexpr int NSLOT = stage_slots<FEAT, SPEC>();
     constexpr int T     = kPairThreads;
     uint4* const  stg0  = smem + threadIdx.x;
     uint4* const  stg1  = smem + NSLOT * T + threadIdx.x;
@@ -587,19 +597,26 @@ __global__ void __launch_bounds__(kPairThreads, DC_FLEX_BLOCKS)
     L.hr  = u0 + 2 < w;
     const float ufac = IN == IN_U16_DEPTH ? p.range_factor.value : 1.0f;
 
+    // Three staging stages: the copies of a row are issued THREE steps before the
+    // row is consumed (two full row steps in flight). With one step of lead the
+    // kernel (3 warps per sub-partition) spent 23 % of its stall samples waiting
+    // for cp.async groups (ncu: long scoreboard at the wait).
     extern __shared__ uint4 smem[];
     constexpr int T    = kPairThreads;
     uint4* const  stg0 = smem + threadIdx.x;
     uint4* const  stg1 = smem + kFlexSlots * T + threadIdx.x;
+    uint4* const  stg2 = smem + 2 * kFlexSlots * T + threadIdx.x;
 
     v3 w0[4], w1[4], w2[4];
     flex_issue(L, max(v0 - 1, 0) * w, v0 >= 1, stg0, T);
     flex_issue(L, v0 * w, true, stg1, T);
     cp_async_commit();
-    cp_async_wait_all();
+    flex_issue(L, min(v0 + 1, h - 1) * w, v0 + 1 < h, stg2, T);
+    cp_async_commit();
+    cp_async_wait_but_one();
     flex_points<IN>(L, ufac, stg0, T, w0);
     flex_points<IN>(L, ufac, stg1, T, w1);
-    flex_issue(L, min(v0 + 1, h - 1) * w, v0 + 1 < h, stg0, T);
+    flex_issue(L, min(v0 + 2, h - 1) * w, v0 + 2 < h, stg0, T);
     cp_async_commit();
 
     using TO         = typename out_elem<OUT>::type;
@@ -607,16 +624,15 @@ __global__ void __launch_bounds__(kPairThreads, DC_FLEX_BLOCKS)
     size_t      oa   = size_t(fa) * p.frame_px + size_t(v0) * w + u0;
     size_t      ob   = size_t(fb) * p.frame_px + size_t(v0) * w + u0;
     const bool  cin0 = u0 >= 1, cin1 = u0 + 1 < w - 1;
-    int         cur = 0, roff = (v0 + 1) * w, v = v0;
-#define DC_FLEX_STEP(UP, MID, DN)                                                              \
+    int         v = v0;
+    // step k = (v - v0) % 3 consumes row v+1 from stage SC and refills stage SN
+    // (consumed in the previous step) with row v+3
+#define DC_FLEX_STEP(UP, MID, DN, SC, SN)                                                      \
     {                                                                                          \
-        uint4* const sc = cur ? stg1 : stg0;                                                   \
-        uint4* const sn = cur ? stg0 : stg1;                                                   \
-        cur ^= 1;                                                                              \
-        cp_async_wait_all();                                                                   \
-        flex_points<IN>(L, ufac, sc, T, DN);                                                   \
-        const bool in2 = v + 2 < h;                                                            \
-        flex_issue(L, in2 ? roff + w : roff - w, in2, sn, T);                                  \
+        cp_async_wait_but_one();                                                               \
+        flex_points<IN>(L, ufac, SC, T, DN);                                                   \
+        const bool in3 = v + 3 < h;                                                            \
+        flex_issue(L, (in3 ? v + 3 : h - 1) * w, in3, SN, T);                                  \
         cp_async_commit();                                                                     \
         const bool rin = v >= 1 && v < h - 1;                                                  \
         f2         f[2];                                                                       \
@@ -644,16 +660,15 @@ __global__ void __launch_bounds__(kPairThreads, DC_FLEX_BLOCKS)
             *reinterpret_cast<float2*>(out + oa) = make_float2(f[0].x, f[1].x);                \
             *reinterpret_cast<float2*>(out + ob) = make_float2(f[0].y, f[1].y);                \
         }                                                                                      \
-        roff += w;                                                                             \
         oa += w;                                                                               \
         ob += w;                                                                               \
         if (++v >= v1)                                                                         \
             break;                                                                             \
     }
     for (;;) {
-        DC_FLEX_STEP(w0, w1, w2)
-        DC_FLEX_STEP(w1, w2, w0)
-        DC_FLEX_STEP(w2, w0, w1)
+        DC_FLEX_STEP(w0, w1, w2, stg2, stg1)
+        DC_FLEX_STEP(w1, w2, w0, stg0, stg2)
+        DC_FLEX_STEP(w2, w0, w1, stg1, stg0)
     }
 #undef DC_FLEX_STEP
     cp_async_wait_all();
