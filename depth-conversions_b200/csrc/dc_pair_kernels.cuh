@@ -353,9 +353,21 @@ template <int FEAT, int SPEC>
 __host__ __device__ constexpr int stage_slots() {
     return kRawSlots + (SPEC == SPEC_UNIFORM ? 0 : tab_slots<FEAT>::n);
 }
+// Staging stages: three (the copies of a row are issued two row steps before
+// the row is consumed: curvature 0.478 -> 0.443 ms) except for max-curve, whose
+// 11 slots per stage would not fit four CTAs per SM three times and which is
+// register bound (the third stage pointer costs it spills).
+template <int FEAT, int SPEC>
+__host__ __device__ constexpr int stages() {
+#ifdef DC_PAIR_STAGES
+    return DC_PAIR_STAGES;
+#else
+    return FEAT == FEAT_MAX_CURVE ? 2 : 3;  // (max-curve measured faster with two)
+#endif
+}
 template <int FEAT, int SPEC>
 constexpr size_t pair_smem_bytes() {
-    return size_t(2) * stage_slots<FEAT, SPEC>() * kPairThreads * sizeof(uint4);
+    return size_t(stages<FEAT, SPEC>()) * stage_slots<FEAT, SPEC>() * kPairThreads * sizeof(uint4);
 }
 
 template <int FEAT, int IN, int OUT, int SPEC>
@@ -400,19 +412,40 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
     extern __shared__ uint4 smem[];
     constexpr int NSLOT = stage_slots<FEAT, SPEC>();
     constexpr int T     = kPairThreads;
+    constexpr int STAGES = stages<FEAT, SPEC>();
     uint4* const  stg0  = smem + threadIdx.x;
     uint4* const  stg1  = smem + NSLOT * T + threadIdx.x;
+    uint4* const  stg2  = smem + 2 * NSLOT * T + threadIdx.x;  // (STAGES == 3 only)
 
+    // A stage holds input row r together with the tables of row r-1 (what the
+    // step that consumes row r as its "down" row needs).
+    auto issue_stage = [&](int r, uint4* st) {
+        const bool in = r < h;
+        issue_raw<R, FC>(L, (in ? r : h - 1) * w, in, st, T);
+        issue_tabs<FEAT, SPEC>(p, r - 1, (r - 1) * w + u0, u0, st + kRawSlots * T, T);
+    };
     wrow<FEAT> up, mid, dn;
     issue_raw<R, FC>(L, max(v0 - 1, 0) * w, v0 >= 1, stg0, T);
     issue_raw<R, FC>(L, v0 * w, true, stg1, T);
     cp_async_commit();
-    cp_async_wait_all();
+    uint4 *sc = stg0, *sf = stg1, *sn = stg1;  // consumed by this step / refilled / consumed next
+    if constexpr (STAGES == 3) {
+        issue_stage(v0 + 1, stg2);
+        cp_async_commit();
+        cp_async_wait_but_one();
+    } else {
+        cp_async_wait_all();
+    }
     commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, stg0, T), up);
     commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, stg1, T), mid);
-    issue_raw<R, FC>(L, min(v0 + 1, h - 1) * w, v0 + 1 < h, stg0, T);
-    issue_tabs<FEAT, SPEC>(p, v0, v0 * w + u0, u0, stg0 + kRawSlots * T, T);
-    cp_async_commit();
+    if constexpr (STAGES == 3) {
+        issue_stage(v0 + 2, stg0);
+        cp_async_commit();
+        sc = stg2, sf = stg1, sn = stg0;
+    } else {
+        issue_stage(v0 + 1, stg0);
+        cp_async_commit();
+    }
 
     pos at;
     at.u0 = u0;
@@ -422,21 +455,32 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
 #pragma unroll
     for (int i = 0; i < 4; ++i)
         col_in[i] = (u0 + i >= 1 && u0 + i < w - 1) ? 1.0f : 0.0f;
-    int cur  = 0;
-    int roff = (v0 + 1) * w;  // row offset of row v + 1
+    int cur  = 0;             // (two stages)
+    int roff = (v0 + 1) * w;  // row offset of row v + 1 (two stages)
 #pragma unroll 1
     for (int v = v0; v < v1; ++v) {
-        uint4* const sc = cur ? stg1 : stg0;  // row v+1 and the tables of row v
-        uint4* const sn = cur ? stg0 : stg1;
-        cur ^= 1;
-        cp_async_wait_all();
-        commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, sc, T), dn);
-        const rtabs<FEAT> tb = fetch_tabs<FEAT, SPEC>(p, sc + kRawSlots * T, T);
-        {
-            const bool in2 = v + 2 < h;
-            issue_raw<R, FC>(L, in2 ? roff + w : roff - w, in2, sn, T);
-            issue_tabs<FEAT, SPEC>(p, v + 1, roff + u0, u0, sn + kRawSlots * T, T);
+        rtabs<FEAT> tb;
+        if constexpr (STAGES == 3) {
+            // sc: row v+1 and the tables of row v
+            cp_async_wait_but_one();
+            commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, sc, T), dn);
+            tb = fetch_tabs<FEAT, SPEC>(p, sc + kRawSlots * T, T);
+            issue_stage(v + 3, sf);
             cp_async_commit();
+            uint4* const consumed = sc;
+            sc = sn, sn = sf, sf = consumed;
+        } else {
+            uint4* const s_now = cur ? stg1 : stg0;  // row v+1 and the tables of row v
+            uint4* const s_nxt = cur ? stg0 : stg1;
+            cur ^= 1;
+            cp_async_wait_all();
+            commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, s_now, T), dn);
+            tb = fetch_tabs<FEAT, SPEC>(p, s_now + kRawSlots * T, T);
+            const bool in2 = v + 2 < h;
+            issue_raw<R, FC>(L, in2 ? roff + w : roff - w, in2, s_nxt, T);
+            issue_tabs<FEAT, SPEC>(p, v + 1, roff + u0, u0, s_nxt + kRawSlots * T, T);
+            cp_async_commit();
+            roff += w;
         }
         at.v               = v;
         const float row_in = (v >= 1 && v < h - 1) ? 1.0f : 0.0f;
@@ -451,7 +495,6 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
             curvature_row<OUT, SPEC>(p, up, mid, dn, tb, at, cc);
         up  = mid;
         mid = dn;
-        roff += w;
         at.oa += w;
         at.ob += w;
     }
