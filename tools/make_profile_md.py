@@ -1,0 +1,67 @@
+#!/usr/bin/env python
+"""profiles/<tag>_bench_and_ncu.md + profiles/r1_traffic.json from the files
+tools/final_profile.sh left under gpurun_out/."""
+import csv, glob, io, json, os, shutil, subprocess, sys
+tag = sys.argv[1] if len(sys.argv) > 1 else "r1z"
+G = "gpurun_out"
+def last_json(path):
+    return json.loads(open(path).read().strip().splitlines()[-1])
+out = [f"# Round 1, final kernels ({tag})", "",
+       "Box: NVIDIA B200, 16 host vCPUs. Produced by `tools/final_profile.sh` (one gpurun call):",
+       "`python bench.py --workload W --steps 20 --warmup 3 --no-cpu-baseline`, the default `python bench.py`,",
+       "`python bench.py --impl reference`, an ncu launch list of the default command and one",
+       "`ncu --set full --clock-control none --import-source on -k regex:pair_kernel|stream_kernel -s 1 -c 1`",
+       "capture per workload (second device-resident launch; same grid as the timed launches).", "",
+       open(f"{G}/{tag}_pytest_gpu.txt").read().strip().splitlines()[-1] + " (`pytest -m gpu` in the same call)", "",
+       "## bench.py (device resident, CUDA events on the launching stream)", "",
+       "| workload | MPix/s | ms/step | GB/s algorithmic | frac of measured HBM peak | e2e MPix/s (host buffers) | clocks |",
+       "|---|---|---|---|---|---|---|"]
+for f in sorted(glob.glob(f"{G}/{tag}_bench_*.json")):
+    if f.endswith("_ref.json") or f.endswith("_default.json"):
+        continue
+    d = last_json(f); r = d["roofline"]; c = d["clocks"]
+    out.append(f"| {d['config']['workload']} | {d['value']:.0f} | {d['ms_per_step']:.4f} | {r['achieved']:.0f} | {r['frac']:.3f} "
+               f"| {d['e2e']['value']:.0f} | {c['sm_mhz']:.0f}/{c['sm_max_mhz']:.0f} MHz, reasons {c['reasons']} |")
+d = last_json(f"{G}/{tag}_bench_default.json"); cb = d["cpu_baseline"]
+out += ["", f"Default line (`python bench.py`, bearing4_960x540): value {d['value']:.0f} MPix/s, e2e {d['e2e']['value']:.0f} MPix/s, "
+        f"cpu_baseline {cb['value']:.1f} MPix/s on {cb['cores']} threads (kind {cb['kind']}; {cb['sample']}).",
+        f"Kernel / CPU = {d['value'] / cb['value']:.0f}x, e2e / CPU = {d['e2e']['value'] / cb['value']:.0f}x.", ""]
+r = last_json(f"{G}/{tag}_bench_ref.json")
+out += [f"`bench.py --impl reference`: {r['value']:.1f} MPix/s, {r['cpu_baseline']['cores']} threads, kind {r['cpu_baseline']['kind']}.", ""]
+want = ['Kernel Name', 'Block Size', 'Grid Size', 'gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum',
+        'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed', 'smsp__inst_executed.sum',
+        'smsp__issue_active.avg.pct_of_peak_sustained_active', 'sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active',
+        'sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active', 'sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active',
+        'sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active', 'sm__warps_active.avg.pct_of_peak_sustained_active',
+        'launch__registers_per_thread', 'launch__shared_mem_per_block_dynamic', 'l1tex__t_sector_pipe_lsu_mem_global_op_ld_hit_rate.pct',
+        'lts__t_sector_hit_rate.pct', 'lts__throughput.avg.pct_of_peak_sustained_elapsed']
+out.append("## ncu --set full (one launch each)")
+traffic = {}
+for wl in ["bearing4_960x540", "flexion_960x540", "curvature_1920x1080", "range_maxcurve_4096x2160", "range_960x540"]:
+    rows = list(csv.reader(io.StringIO(open(f"{G}/{tag}_ncu_{wl}_raw.csv").read())))
+    hdr, units, vals = rows[0], rows[1], rows[2]
+    def get(k):
+        i = hdr.index(k); v = float(vals[i].replace(",", ""))
+        return v * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}.get(units[i], 1)
+    out += ["", f"### {wl}", "", "| metric | value | unit |", "|---|---|---|"]
+    for w_ in want:
+        if w_ in hdr:
+            i = hdr.index(w_); out.append(f"| {w_} | {vals[i]} | {units[i]} |")
+    rd, wr = get('dram__bytes_read.sum'), get('dram__bytes_write.sum')
+    alg = last_json(f"{G}/{tag}_bench_{wl}.json")["roofline"]["algorithmic_bytes_per_launch"]
+    traffic[wl] = {"dram_bytes": rd + wr, "dram_read": rd, "dram_write": wr, "algorithmic_bytes": alg,
+                   "kernel": vals[hdr.index('Kernel Name')], "source": f"profiles/{tag}_bench_and_ncu.md ({wl})"}
+    out.append(f"| DRAM traffic / algorithmic bytes | {(rd + wr) / alg:.3f} | |")
+    s = subprocess.run([sys.executable, "tools/ncu_summary.py", f"{G}/{tag}_ncu_{wl}", "6"], capture_output=True, text=True).stdout
+    st = [l for l in s.splitlines() if l.startswith("barrier=")]
+    if st:
+        out += ["", "stall samples: " + st[0]]
+out += ["", "Reading: the stencil kernels are bound by FP32 work (register-file operand bandwidth, DESIGN.md section 3),",
+        "not by HBM: DRAM throughput 8-40 %, DRAM traffic = the algorithmic bytes (tables from L2, halos from L1).",
+        "The streaming range kernel is HBM bound."]
+open(f"profiles/{tag}_bench_and_ncu.md", "w").write("\n".join(out) + "\n")
+json.dump(traffic, open("profiles/r1_traffic.json", "w"), indent=1)
+shutil.copy(f"{G}/{tag}_launches_bearing4.csv", f"profiles/{tag}_launches_bearing4_960x540.csv")
+print("\n".join(out[8:24]))
+for k, v in traffic.items():
+    print(k, round(v["dram_bytes"] / v["algorithmic_bytes"], 3))

@@ -1,7 +1,12 @@
 """Summarise an .ncu-rep: headline metrics, stall totals, hottest instructions."""
 import csv, io, subprocess, sys
 rep = sys.argv[1]; ntop = int(sys.argv[2]) if len(sys.argv) > 2 else 25
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+def page(name):
+    """rep may be an .ncu-rep or the prefix of exported <prefix>_raw.csv / <prefix>_source.csv"""
+    if rep.endswith(".ncu-rep"):
+        return subprocess.run(["ncu", "-i", rep, "--page", name, "--csv"], capture_output=True, text=True).stdout
+    return open(f"{rep}_{name}.csv").read()
+raw = page("raw")
 rows = list(csv.reader(io.StringIO(raw))); hdr, units, vals = rows[0], rows[1], rows[2]
 KEYS = ['Kernel Name', 'Grid Size', 'gpu__time_duration.sum', 'smsp__inst_executed.sum', 'launch__registers_per_thread',
         'smsp__issue_active.avg.pct_of_peak_sustained_active', 'sm__warps_active.avg.pct_of_peak_sustained_active',
@@ -15,7 +20,7 @@ KEYS = ['Kernel Name', 'Grid Size', 'gpu__time_duration.sum', 'smsp__inst_execut
 for k in KEYS:
     if k in hdr:
         i = hdr.index(k); print(f"{k} = {vals[i]} {units[i]}")
-src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+src = page("source")
 rows = list(csv.reader(io.StringIO(src))); hdr, body = rows[1], rows[2:]
 g = hdr.index
 names = [h for h in hdr if h.startswith("stall_") and "Not Issued" not in h]
