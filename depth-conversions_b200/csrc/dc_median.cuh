@@ -8,11 +8,10 @@
 // A thread owns two adjacent columns and marches down a strip of rows with the
 // last K rows of its K+1 columns in registers. u16 pixels travel as u16x2
 // pairs (one pair per window column: (px[u+c], px[u+1+c])), so that one
-// VIMNMX.U16x2 orders the window entry of both output pixels. The median is
-// found by "forgetful selection": keep ceil(n/2)+1 candidates, drop their
-// minimum and maximum, take in the next element, until one is left. The
-// minimum / maximum searches are built from compare-exchanges, so the scheme
-// is correct by construction for any n.
+// VIMNMX.U16x2 orders the window entry of both output pixels. The 3x3 median is
+// found by "forgetful selection" (keep n/2+2 candidates, drop their minimum and
+// maximum, take in the next element, until one is left: correct by construction),
+// the 5x5 median by a 99-exchange selection network verified exhaustively.
 #ifndef DC_MEDIAN_CUH
 #define DC_MEDIAN_CUH
 
@@ -71,14 +70,44 @@ struct select {
     }
 };
 
+// Median of 25 by a 99-exchange selection network (the classic opt_med25
+// sequence). tests/test_median_network.py parses this table and checks it
+// exhaustively with the zero-one principle (all 2^25 inputs). Exchanges whose
+// minimum or maximum is never read again lose that half to dead-code elimination.
+// MEDIAN25_NETWORK_BEGIN
+__device__ constexpr unsigned char kNet25[99][2] = {
+    {0, 1},   {3, 4},   {2, 4},   {2, 3},   {6, 7},   {5, 7},   {5, 6},   {9, 10},  {8, 10},
+    {8, 9},   {12, 13}, {11, 13}, {11, 12}, {15, 16}, {14, 16}, {14, 15}, {18, 19}, {17, 19},
+    {17, 18}, {21, 22}, {20, 22}, {20, 21}, {23, 24}, {2, 5},   {3, 6},   {0, 6},   {0, 3},
+    {4, 7},   {1, 7},   {1, 4},   {11, 14}, {8, 14},  {8, 11},  {12, 15}, {9, 15},  {9, 12},
+    {13, 16}, {10, 16}, {10, 13}, {20, 23}, {17, 23}, {17, 20}, {21, 24}, {18, 24}, {18, 21},
+    {19, 22}, {8, 17},  {9, 18},  {0, 18},  {0, 9},   {10, 19}, {1, 19},  {1, 10},  {11, 20},
+    {2, 20},  {2, 11},  {12, 21}, {3, 21},  {3, 12},  {13, 22}, {4, 22},  {4, 13},  {14, 23},
+    {5, 23},  {5, 14},  {15, 24}, {6, 24},  {6, 15},  {7, 16},  {7, 19},  {13, 21}, {15, 23},
+    {7, 13},  {7, 15},  {1, 9},   {3, 11},  {5, 17},  {11, 17}, {9, 17},  {4, 10},  {6, 12},
+    {7, 14},  {4, 6},   {4, 7},   {12, 14}, {10, 14}, {6, 7},   {10, 12}, {6, 10},  {6, 17},
+    {12, 17}, {7, 17},  {7, 10},  {12, 18}, {7, 12},  {10, 18}, {12, 20}, {10, 20}, {10, 12}};
+// MEDIAN25_NETWORK_END  (result: element 12)
+
 template <int K, typename T>
 __device__ __forceinline__ T median_of(const T (&w)[K * K]) {
-    constexpr int n = K * K, live = n / 2 + 2;  // 9 -> 6, 25 -> 14
-    T             cand[live];
+    if constexpr (K == 5) {
+        T v[25];
 #pragma unroll
-    for (int i = 0; i < live; ++i)
-        cand[i] = w[i];
-    return select<n, live, T>::run(cand, w, live);
+        for (int i = 0; i < 25; ++i)
+            v[i] = w[i];
+#pragma unroll
+        for (int i = 0; i < 99; ++i)
+            cex(v[kNet25[i][0]], v[kNet25[i][1]]);
+        return v[12];
+    } else {
+        constexpr int n = K * K, live = n / 2 + 2;  // 9 -> 6
+        T             cand[live];
+#pragma unroll
+        for (int i = 0; i < live; ++i)
+            cand[i] = w[i];
+        return select<n, live, T>::run(cand, w, live);
+    }
 }
 
 // ---- u16 -------------------------------------------------------------------
