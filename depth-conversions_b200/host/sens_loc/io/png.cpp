@@ -1,5 +1,7 @@
 #include "png.h"
 
+#include "fast_deflate.h"
+
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -154,7 +156,11 @@ status encode_grey(const void* src, int w, int h, int bit_depth, std::vector<uns
         return status::unsupported;
     const std::size_t bpp = std::size_t(bit_depth / 8), row = std::size_t(w) * bpp;
     const std::size_t raw_size = (row + 1) * std::size_t(h);
-    const uLong       bound    = compressBound(uLong(raw_size));
+    // DC_PNG_ZLIB=1 in the environment: zlib level-1 / Z_RLE (what cv::imwrite
+    // produces) instead of the run-length + Huffman encoder of fast_deflate.cpp
+    static const bool use_zlib = std::getenv("DC_PNG_ZLIB") != nullptr;
+    const uLong       bound    = uLong(std::max<std::size_t>(compressBound(uLong(raw_size)),
+                                                             rle_deflate_bound(raw_size)));
     scratch.resize(raw_size + bound);
     unsigned char*       raw = scratch.data();
     unsigned char*       zed = scratch.data() + raw_size;
@@ -165,12 +171,19 @@ status encode_grey(const void* src, int w, int h, int bit_depth, std::vector<uns
         line[0]                   = 1;
         unsigned char* cur        = line + 1;
         if (bpp == 2) {
-            unsigned pl = 0, ph = 0;
-            for (std::size_t i = 0; i < row; i += 2) {
-                const unsigned hi = s[i + 1], lo = s[i];
-                cur[i]     = (unsigned char)(hi - ph);
-                cur[i + 1] = (unsigned char)(lo - pl);
-                ph = hi, pl = lo;
+            // per pixel, no loop-carried state (vectorisable): the two bytes of the
+            // big-endian sample minus the bytes of the previous sample
+            const auto* px = reinterpret_cast<const unsigned short*>(s);
+            unsigned    x0 = px[0];
+            cur[0] = (unsigned char)(x0 >> 8), cur[1] = (unsigned char)x0;
+#if defined(__GNUC__)
+#pragma GCC ivdep
+#endif
+            for (std::size_t k = 1; k < std::size_t(w); ++k) {
+                const unsigned x = px[k], p = px[k - 1];
+                const unsigned hi = ((x >> 8) - (p >> 8)) & 0xffu, lo = (x - p) & 0xffu;
+                const unsigned short o = (unsigned short)(hi | (lo << 8));
+                std::memcpy(cur + 2 * k, &o, 2);
             }
         } else {
             unsigned p = 0;
@@ -180,18 +193,23 @@ status encode_grey(const void* src, int w, int h, int bit_depth, std::vector<uns
             }
         }
     }
-    z_stream zs{};
-    if (deflateInit2(&zs, level, Z_DEFLATED, 15, 8, Z_RLE) != Z_OK)
-        return status::corrupt;
-    zs.next_in   = raw;
-    zs.avail_in  = uInt(raw_size);
-    zs.next_out  = zed;
-    zs.avail_out = uInt(bound);
-    const int zr = deflate(&zs, Z_FINISH);
-    const std::size_t zn = zs.total_out;
-    deflateEnd(&zs);
-    if (zr != Z_STREAM_END)
-        return status::corrupt;
+    std::size_t zn = 0;
+    if (!use_zlib) {
+        zn = rle_deflate(raw, raw_size, zed);
+    } else {
+        z_stream zs{};
+        if (deflateInit2(&zs, level, Z_DEFLATED, 15, 8, Z_RLE) != Z_OK)
+            return status::corrupt;
+        zs.next_in   = raw;
+        zs.avail_in  = uInt(raw_size);
+        zs.next_out  = zed;
+        zs.avail_out = uInt(bound);
+        const int zr = deflate(&zs, Z_FINISH);
+        zn           = zs.total_out;
+        deflateEnd(&zs);
+        if (zr != Z_STREAM_END)
+            return status::corrupt;
+    }
 
     out.clear();
     out.reserve(zn + 64);

@@ -93,6 +93,17 @@ def test_png_codec_roundtrip(tmp_path):
         "ramp": (np.arange(540 * 960, dtype=np.uint32).reshape(540, 960) % 65536).astype(np.uint16),
         "one": np.array([[65535]], np.uint16),
         "zeros": np.zeros((5, 1), np.uint16),
+        # the writer's own deflate encoder (io/fast_deflate.cpp): several 256 KB blocks,
+        # runs that cross block boundaries, incompressible blocks (stored), run lengths
+        # around the 258 limit, a constant image
+        "big_zeros": np.zeros((540, 960), np.uint16),
+        "big_noise": rng.integers(0, 65536, (540, 960), dtype=np.uint16),
+        "constant": np.full((300, 500), 0x1234, np.uint16),
+        "holes": np.where(rng.random((540, 960)) < 0.3, 0,
+                          rng.integers(700, 2600, (540, 960))).astype(np.uint16),
+        "runs": np.repeat(rng.integers(0, 65536, (64, 40), dtype=np.uint16),
+                          rng.integers(1, 300, 40), axis=1),
+        "blocky": np.kron(rng.integers(0, 3, (34, 60)), np.ones((16, 16), np.int64)).astype(np.uint16) * 999,
     }
     for name, img in cases.items():
         a, b = str(tmp_path / f"{name}_a.png"), str(tmp_path / f"{name}_b.png")
@@ -125,3 +136,34 @@ def test_no_cpu_fallback(work):
     assert "no CUDA device" in r.stderr or "CUDA" in r.stderr
     assert "Could not process index \"0\"" in r.stderr
     assert not os.path.exists(os.path.join(work, "out0.png"))
+
+
+def test_png_writer_deflate_fuzz(tmp_path):
+    """io/fast_deflate.cpp (run-length + dynamic Huffman) through the PNG writer,
+    decoded by OpenCV (libpng + zlib inflate): random sizes and run structures."""
+    rs = np.random.RandomState(1)
+    a, b = str(tmp_path / "a.png"), str(tmp_path / "b.png")
+    for t in range(24):
+        h, w = rs.randint(1, 200), rs.randint(1, 700)
+        kind = t % 6
+        if kind == 0:
+            img = rs.randint(0, 65536, (h, w))
+        elif kind == 1:
+            img = np.zeros((h, w))
+        elif kind == 2:
+            img = np.repeat(rs.randint(0, 65536, (h, 1)), w, axis=1)
+        elif kind == 3:
+            img = np.where(rs.rand(h, w) < 0.5, 0, rs.randint(0, 4, (h, w)) * 257)
+        elif kind == 4:
+            img = np.cumsum(rs.randint(0, 2, (h, w)), axis=1) * 3
+        else:
+            img = np.kron(rs.randint(0, 65536, (h // 8 + 1, w // 8 + 1)), np.ones((8, 8), np.int64))[:h, :w]
+        img = img.astype(np.uint16)
+        cv2.imwrite(a, img)
+        assert subprocess.run([SELFTEST, "png", a, b]).returncode == 0
+        back = cv2.imread(b, cv2.IMREAD_UNCHANGED)
+        assert back is not None and back.shape == img.shape and np.array_equal(back, img), (t, kind, h, w)
+    # the zlib path stays selectable
+    env = dict(os.environ, DC_PNG_ZLIB="1")
+    assert subprocess.run([SELFTEST, "png", a, b], env=env).returncode == 0
+    assert np.array_equal(cv2.imread(b, cv2.IMREAD_UNCHANGED), img)
