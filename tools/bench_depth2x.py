@@ -78,10 +78,22 @@ def main():
             assert r.returncode == 0, r.stdout + r.stderr
             best = dt if best is None else min(best, dt)
         inner = [l.strip() for l in (r.stdout + r.stderr).splitlines() if "took" in l]
+        # the pipeline alone (reader/GPU/writer stages, without CUDA start-up, which varies
+        # between 0.2 s and 4 s on a fresh box): DEPTH2X_PROFILE timestamps
+        rp = subprocess.run(cmd, cwd=work, capture_output=True, text=True,
+                            env=dict(os.environ, DEPTH2X_PROFILE="1"))
+        marks = {}
+        for l in rp.stderr.splitlines():
+            if l.startswith("[profile"):
+                t = float(l[len("[profile"):l.index("s]")])
+                marks[l[l.index("]") + 2:].rsplit(" ", 1)[0]] = t
+        pipe = marks.get("pipeline drained", 0.0) - marks.get("dc_create end", 0.0)
         print(json.dumps({"arm": "depth2x (B200)", "feature": feat, "size": a.size, "frames": a.frames,
                           "devices": a.devices, "wall_s": best, "frames_per_s": a.frames / best,
                           "mpix_per_s": a.frames * w * h / best / 1e6, "host_threads": ncpu,
-                          "png_in_mb": in_bytes / 1e6, "tool_says": inner[-1] if inner else ""}), flush=True)
+                          "png_in_mb": in_bytes / 1e6, "tool_says": inner[-1] if inner else "",
+                          "pipeline_s": pipe, "pipeline_mpix_per_s": a.frames * w * h / pipe / 1e6 if pipe > 0 else None,
+                          "cuda_startup_s": marks.get("dc_create end", 0.0)}), flush=True)
         if a.no_cpu or not ref_available():
             continue
         # ---- CPU arm: the reference's per-index work, frame parallel ----
