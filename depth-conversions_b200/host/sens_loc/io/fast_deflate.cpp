@@ -5,7 +5,6 @@
 #include <cstring>
 #include <vector>
 
-#include <zlib.h>  // adler32 only
 
 namespace sens_loc::io {
 namespace {
@@ -340,7 +339,7 @@ std::size_t rle_deflate(const unsigned char* in, std::size_t n, unsigned char* o
         pos += blk;
     } while (pos < n);
     bw.align_byte();
-    const uLong a = adler32(adler32(0L, Z_NULL, 0), in, uInt(n));
+    const std::uint32_t a = adler32_fast(1, in, n);
     bw.p[0] = (unsigned char)(a >> 24), bw.p[1] = (unsigned char)(a >> 16);
     bw.p[2] = (unsigned char)(a >> 8), bw.p[3] = (unsigned char)a;
     return std::size_t(bw.p + 4 - out);

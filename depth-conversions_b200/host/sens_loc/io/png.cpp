@@ -2,13 +2,19 @@
 
 #include "fast_deflate.h"
 
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <zlib.h>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 
 namespace sens_loc::io::png {
 namespace {
+
+std::atomic<unsigned long> g_fast{0}, g_zlib{0};
 
 const unsigned char kSig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
 
@@ -34,6 +40,39 @@ void chunk(std::vector<unsigned char>& out, const char type[4], const unsigned c
 int paeth(int a, int b, int c) {
     const int p = a + b - c, pa = std::abs(p - a), pb = std::abs(p - b), pc = std::abs(p - c);
     return (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
+}
+
+
+// Filter type 1 (sub) for 16 bit samples: every byte is the sum of the bytes two
+// positions apart up to here. Writes the un-filtered big-endian row back to `cur`
+// (the next row's filter may look at it) and the little-endian samples to `o`.
+void unsub16(unsigned char* cur, unsigned char* o, std::size_t w) {
+    std::size_t k = 0;
+#if defined(__SSE2__)
+    __m128i carry = _mm_setzero_si128();  // the previous pixel in all eight lanes
+    for (; k + 8 <= w; k += 8) {
+        __m128i v = _mm_loadu_si128(reinterpret_cast<const __m128i*>(cur + 2 * k));
+        v         = _mm_add_epi8(v, _mm_slli_si128(v, 2));  // byte-wise prefix sums over 8 pixels
+        v         = _mm_add_epi8(v, _mm_slli_si128(v, 4));
+        v         = _mm_add_epi8(v, _mm_slli_si128(v, 8));
+        v         = _mm_add_epi8(v, carry);
+        _mm_storeu_si128(reinterpret_cast<__m128i*>(cur + 2 * k), v);
+        _mm_storeu_si128(reinterpret_cast<__m128i*>(o + 2 * k),
+                         _mm_or_si128(_mm_slli_epi16(v, 8), _mm_srli_epi16(v, 8)));
+        carry = _mm_shuffle_epi32(_mm_shufflehi_epi16(v, 0xff), 0xff);
+    }
+    unsigned hi = k != 0 ? cur[2 * k - 2] : 0u, lo = k != 0 ? cur[2 * k - 1] : 0u;
+#else
+    unsigned hi = 0, lo = 0;
+#endif
+    for (; k < w; ++k) {
+        hi             = (hi + cur[2 * k]) & 0xffu;
+        lo             = (lo + cur[2 * k + 1]) & 0xffu;
+        cur[2 * k]     = (unsigned char)hi;
+        cur[2 * k + 1] = (unsigned char)lo;
+        o[2 * k]       = (unsigned char)lo;
+        o[2 * k + 1]   = (unsigned char)hi;
+    }
 }
 
 }  // namespace
@@ -77,32 +116,59 @@ status decode_grey(const std::vector<unsigned char>& bytes, const info& hdr, voi
     const std::size_t raw_size = (row + 1) * std::size_t(hdr.h);
     scratch.resize(raw_size);
 
-    z_stream zs{};
-    if (inflateInit(&zs) != Z_OK)
-        return status::corrupt;
-    zs.next_out  = scratch.data();
-    zs.avail_out = uInt(raw_size);
-    int         zr  = Z_OK;
-    std::size_t pos = 8;
-    bool        end = false;
-    while (!end && pos + 12 <= bytes.size()) {
-        const std::uint32_t  len  = be32(bytes.data() + pos);
-        const unsigned char* type = bytes.data() + pos + 4;
-        if (pos + 12 + len > bytes.size())
-            break;
-        if (std::memcmp(type, "IDAT", 4) == 0 && zr == Z_OK) {
-            zs.next_in  = const_cast<unsigned char*>(type + 4);
-            zs.avail_in = len;
-            zr          = inflate(&zs, Z_NO_FLUSH);
-        } else if (std::memcmp(type, "IEND", 4) == 0) {
-            end = true;
+    // Fast path: gather the IDAT payloads (libpng writes 8 KB chunks) and decode the
+    // zlib stream in one go with the table-driven inflate of fast_inflate.cpp, which
+    // also verifies the Adler-32 trailer. Anything it does not like -> zlib below.
+    // DC_PNG_ZLIB=1 in the environment skips the fast path.
+    static const bool zlib_only = std::getenv("DC_PNG_ZLIB") != nullptr;
+    bool              complete  = false;
+    if (!zlib_only) {
+        static thread_local std::vector<unsigned char> idat;
+        idat.clear();
+        std::size_t pos = 8;
+        while (pos + 12 <= bytes.size()) {
+            const std::uint32_t  len  = be32(bytes.data() + pos);
+            const unsigned char* type = bytes.data() + pos + 4;
+            if (pos + 12 + len > bytes.size() || std::memcmp(type, "IEND", 4) == 0)
+                break;
+            if (std::memcmp(type, "IDAT", 4) == 0)
+                idat.insert(idat.end(), type + 4, type + 4 + len);
+            pos += 12 + len;
         }
-        pos += 12 + len;
+        const std::size_t n = idat.size();
+        idat.resize(n + 32, 0);  // fast_inflate reads whole words past the end
+        complete = fast_inflate(idat.data(), n, scratch.data(), raw_size);
     }
-    const bool complete = zs.total_out == raw_size && (zr == Z_STREAM_END || zr == Z_OK);
-    inflateEnd(&zs);
+    const bool via_zlib = !complete;
+    if (via_zlib) {
+        z_stream zs{};
+        if (inflateInit(&zs) != Z_OK)
+            return status::corrupt;
+        zs.next_out  = scratch.data();
+        zs.avail_out = uInt(raw_size);
+        int         zr  = Z_OK;
+        std::size_t pos = 8;
+        bool        end = false;
+        while (!end && pos + 12 <= bytes.size()) {
+            const std::uint32_t  len  = be32(bytes.data() + pos);
+            const unsigned char* type = bytes.data() + pos + 4;
+            if (pos + 12 + len > bytes.size())
+                break;
+            if (std::memcmp(type, "IDAT", 4) == 0 && zr == Z_OK) {
+                zs.next_in  = const_cast<unsigned char*>(type + 4);
+                zs.avail_in = len;
+                zr          = inflate(&zs, Z_NO_FLUSH);
+            } else if (std::memcmp(type, "IEND", 4) == 0) {
+                end = true;
+            }
+            pos += 12 + len;
+        }
+        complete = zs.total_out == raw_size && (zr == Z_STREAM_END || zr == Z_OK);
+        inflateEnd(&zs);
+    }
     if (!complete)
         return status::corrupt;
+    (via_zlib ? g_zlib : g_fast).fetch_add(1, std::memory_order_relaxed);
 
     unsigned char*       out  = static_cast<unsigned char*>(dst);
     const unsigned char* prev = nullptr;
@@ -110,6 +176,12 @@ status decode_grey(const std::vector<unsigned char>& bytes, const info& hdr, voi
         unsigned char* line = scratch.data() + std::size_t(y) * (row + 1);
         const int      ft   = line[0];
         unsigned char* cur  = line + 1;
+        unsigned char* o = out + std::size_t(y) * row;
+        if (ft == 1 && bpp == 2) {  // the common case, un-filtered and byte-swapped in one pass
+            unsub16(cur, o, std::size_t(hdr.w));
+            prev = cur;
+            continue;
+        }
         switch (ft) {
         case 0: break;
         case 1:
@@ -136,11 +208,12 @@ status decode_grey(const std::vector<unsigned char>& bytes, const info& hdr, voi
             break;
         default: return status::corrupt;
         }
-        unsigned char* o = out + std::size_t(y) * row;
         if (bpp == 2) {
-            for (std::size_t i = 0; i < row; i += 2) {  // big endian -> native (little endian)
-                o[i]     = cur[i + 1];
-                o[i + 1] = cur[i];
+            for (std::size_t k = 0; k < std::size_t(hdr.w); ++k) {  // big endian -> little endian
+                unsigned short v;
+                std::memcpy(&v, cur + 2 * k, 2);
+                v = (unsigned short)((v >> 8) | (v << 8));
+                std::memcpy(o + 2 * k, &v, 2);
             }
         } else {
             std::memcpy(o, cur, row);
@@ -149,6 +222,8 @@ status decode_grey(const std::vector<unsigned char>& bytes, const info& hdr, voi
     }
     return status::ok;
 }
+
+decode_counts decode_statistics() { return {g_fast.load(), g_zlib.load()}; }
 
 status encode_grey(const void* src, int w, int h, int bit_depth, std::vector<unsigned char>& out,
                    std::vector<unsigned char>& scratch, int level) {

@@ -30,6 +30,13 @@ status read_file(const std::string& path, std::vector<unsigned char>& bytes, inf
 status decode_grey(const std::vector<unsigned char>& bytes, const info& hdr, void* dst,
                    std::vector<unsigned char>& scratch);
 
+/// How many successful decodes of this process went through io::fast_inflate and how
+/// many through zlib's inflate (its fallback). For tests and diagnostics.
+struct decode_counts {
+    unsigned long fast, zlib;
+};
+decode_counts decode_statistics();
+
 /// Encodes w*h greyscale samples (bit_depth 8 or 16) as PNG: filter "sub",
 /// zlib level `level` with the RLE strategy (what OpenCV's imwrite uses).
 status encode_grey(const void* src, int w, int h, int bit_depth, std::vector<unsigned char>& out,

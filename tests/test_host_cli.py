@@ -167,3 +167,43 @@ def test_png_writer_deflate_fuzz(tmp_path):
     env = dict(os.environ, DC_PNG_ZLIB="1")
     assert subprocess.run([SELFTEST, "png", a, b], env=env).returncode == 0
     assert np.array_equal(cv2.imread(b, cv2.IMREAD_UNCHANGED), img)
+
+
+def test_png_reader_inflate_fuzz():
+    """io/fast_inflate.cpp (the PNG reader's table-driven inflate) against streams zlib
+    writes at every level / strategy / window / flush pattern, from all-literal to
+    all-match data; damaged streams are refused or accepted exactly as zlib does."""
+    for seed, iters, env in ((1, 500, None), (2, 500, dict(os.environ, DC_INFLATE_SCALAR="1"))):
+        r = subprocess.run([SELFTEST, "inflatefuzz", str(seed), str(iters)], capture_output=True, text=True,
+                           env=env)
+        assert r.returncode == 0 and r.stdout.startswith("ok %d " % iters), r.stdout + r.stderr
+
+
+def test_png_reader_other_writers(tmp_path):
+    """The reader on files from other encoders: libpng at every compression level and
+    zlib strategy (many 8 KB IDAT chunks, all five row filters), PIL (one big IDAT), and a
+    truncated file (refused by both the fast path and the zlib fallback)."""
+    rng = np.random.default_rng(3)
+    y, x = np.mgrid[0:270, 0:480]
+    img = (3000 + 800 * np.sin(x / 37.0) + 500 * np.cos(y / 23.0) + rng.normal(0, 5, x.shape)).astype(np.uint16)
+    img[rng.random(img.shape) < 0.05] = 0
+    img[100:140, 200:330] = 0
+    a, b = str(tmp_path / "a.png"), str(tmp_path / "b.png")
+    strategies = [cv2.IMWRITE_PNG_STRATEGY_DEFAULT, cv2.IMWRITE_PNG_STRATEGY_FILTERED,
+                  cv2.IMWRITE_PNG_STRATEGY_HUFFMAN_ONLY, cv2.IMWRITE_PNG_STRATEGY_RLE,
+                  cv2.IMWRITE_PNG_STRATEGY_FIXED]
+    for level in range(10):
+        for strategy in strategies:
+            assert cv2.imwrite(a, img, [cv2.IMWRITE_PNG_COMPRESSION, level, cv2.IMWRITE_PNG_STRATEGY, strategy])
+            for env, which in ((None, "fast"), (dict(os.environ, DC_PNG_ZLIB="1"), "zlib")):
+                r = subprocess.run([SELFTEST, "png", a, b], env=env, capture_output=True, text=True)
+                # (the fast path must take these itself, not lean on its fallback)
+                assert r.returncode == 0 and r.stdout.strip() == "inflate " + which, (level, strategy, r.stdout)
+                assert np.array_equal(cv2.imread(b, cv2.IMREAD_UNCHANGED), img), (level, strategy)
+    from PIL import Image
+    Image.fromarray(img).save(a, compress_level=9)
+    assert subprocess.run([SELFTEST, "png", a, b]).returncode == 0
+    assert np.array_equal(cv2.imread(b, cv2.IMREAD_UNCHANGED), img)
+    data = open(a, "rb").read()
+    open(a, "wb").write(data[: len(data) // 2])
+    assert subprocess.run([SELFTEST, "png", a, b]).returncode != 0
