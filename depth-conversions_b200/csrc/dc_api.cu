@@ -328,6 +328,30 @@ cudaError_t launch_pair(const dc::kparams& p, int n_frames, cudaStream_t s) {
         return e != nullptr ? std::atoi(e) : -1;
     }();
     const int spec = forced == 0 ? 0 : pair_spec<FEAT, IN>(p);
+    if constexpr (FEAT == dc::FEAT_MAX_CURVE) {
+        // One scalar for all four neighbour-angle tables (1080p and larger with
+        // Kinect-like intrinsics): the kernel that computes every pixel-pair edge
+        // once for both of its ends (dc_pair_kernels.cuh maxcurve_edge_kernel).
+        static const int edge_rows = [] {
+            const char* e = std::getenv("DC_MCE_ROWS");  // 0 disables the kernel
+            return e != nullptr ? std::atoi(e) : 36;
+        }();
+        auto bits = [](float v) {
+            unsigned u;
+            std::memcpy(&u, &v, sizeof u);
+            return u;
+        };
+        const unsigned c0 = bits(p.cosp[0].value);
+        if (spec == dc::pr::SPEC_UNIFORM && edge_rows >= 3 && c0 == bits(p.cosp[1].value) &&
+            c0 == bits(p.cosp[2].value) && c0 == bits(p.cosp[3].value)) {
+            const long long estrips  = (p.h + edge_rows - 1) / edge_rows;
+            const long long ethreads = pairs * estrips * (p.w / 4);
+            const long long eblocks  = (ethreads + dc::pr::kPairThreads - 1) / dc::pr::kPairThreads;
+            dc::pr::maxcurve_edge_kernel<IN, OUT>
+                <<<unsigned(eblocks), block, dc::pr::mce_smem_bytes(), s>>>(p, n_frames, edge_rows);
+            return cudaGetLastError();
+        }
+    }
     switch (spec) {
     case dc::pr::SPEC_TABLES:
         dc::pr::pair_kernel<FEAT, IN, OUT, dc::pr::SPEC_TABLES>

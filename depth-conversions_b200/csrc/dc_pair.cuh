@@ -50,7 +50,19 @@ __device__ __forceinline__ f2 rcp2(f2 x) { return make_float2(mufu_rcp(x.x), muf
 __device__ __forceinline__ float halve(float x) {
     return __uint_as_float(__float_as_uint(x) - 0x00800000u);
 }
-__device__ __forceinline__ f2 halve2(f2 x) { return make_float2(halve(x.x), halve(x.y)); }
+// Measured (profiles/r1_ab_experiments.md): one FMUL2 by 0.5 instead of the two
+// integer adds makes bearing 4 % and curvature 2 % SLOWER although it removes an
+// instruction: the row loops are bound by FMA-pipe slots, ALU-pipe work is hidden.
+#ifndef DC_HALVE_ALU
+#define DC_HALVE_ALU 1
+#endif
+__device__ __forceinline__ f2 halve2(f2 x) {
+#if DC_HALVE_ALU
+    return make_float2(halve(x.x), halve(x.y));
+#else
+    return mul2(x, B(0.5f));
+#endif
+}
 
 // RN(sqrt(x)) per half (dc_fastmath.cuh sqrt_rn_fast), y = the rsqrt seed.
 __device__ __forceinline__ f2 sqrt2(f2 x, f2& y) {
@@ -89,6 +101,21 @@ __device__ __forceinline__ f2 acos_abs2(f2 q) {
     return mul2(s, p);
 }
 #define DC_PI_F 3.14159274101257324f
+// u16 reflection without compares (bearing epilogue; DC_REFLECT_FSEL=0, measured
+// 1.5 % slower than the compare + select form, see halve2): for the ratio q
+//   sign_xor(Q, q)  = q < 0 ? -Q : Q             (one LOP3)
+//   magic_refl(q)   = q < 0 ? M + 65535 : M      (one PRMT: the low two bytes
+//                     replicate q's sign bit, M = 1.5 * 2^23 = 0x4B400000)
+// so that (q < 0 ? pi - r : r) * Q + M = r * sign_xor(Q, q) + magic_refl(q) with
+// pi * Q = 65535. A ratio of -0 cannot occur (RN(b - x) is +0 when b == x).
+__device__ __forceinline__ float sign_xor(float v, float q) {
+    return __uint_as_float(__float_as_uint(v) ^ (__float_as_uint(q) & 0x80000000u));
+}
+__device__ __forceinline__ float magic_refl(float q) {
+    unsigned d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(__float_as_uint(q)), "r"(0x4B400000u), "r"(0x76BBu));
+    return __uint_as_float(d);
+}
 __device__ __forceinline__ f2 reflect2(f2 r, f2 q) {
     const f2 m = sub2(B(DC_PI_F), r);
     return make_float2(q.x < 0.0f ? m.x : r.x, q.y < 0.0f ? m.y : r.y);

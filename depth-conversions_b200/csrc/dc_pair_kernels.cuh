@@ -4,10 +4,21 @@
 
 #include "dc_pair.cuh"
 
+#include <type_traits>
+
 namespace dc {
 namespace pr {
 
 constexpr int kPairThreads = 128;
+#ifndef DC_REFLECT_FSEL
+#define DC_REFLECT_FSEL 1
+#endif
+// Features whose three-stage row loop is instantiated three times with the
+// window rows / stages renamed instead of rotated (bit mask over FEAT_*).
+// Measured: curvature 0.443 -> 0.429 ms, bearing 0.605 -> 0.615 ms (kept rotating).
+#ifndef DC_PAIR_RENAME_MASK
+#define DC_PAIR_RENAME_MASK (1 << FEAT_CURVATURE)
+#endif
 
 // One window row: range of columns u0-1 .. u0+4 of both frames, plus (curvature
 // only) the minimum over each 3-column neighbourhood for the "any of the nine
@@ -166,10 +177,16 @@ __device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BE
                 // and rounding afterwards this moves a result by at most one LSB
                 // (tolerance of the quantised images: +-1 LSB; acos itself is
                 // only 1e-6 accurate against glibc).
-                const float Q = p.q_bearing, M = 12582912.0f, C = fmaf(DC_PI_F, Q, M);
+                const float Q = p.q_bearing, M = 12582912.0f;
+#if DC_REFLECT_FSEL
+                const float C  = fmaf(DC_PI_F, Q, M);
                 const bool  na = k.q.x < 0.0f, nb = k.q.y < 0.0f;
                 const f2    sq  = make_float2(na ? -Q : Q, nb ? -Q : Q);
                 const f2    off = make_float2(na ? C : M, nb ? C : M);
+#else
+                const f2 sq  = make_float2(sign_xor(Q, k.q.x), sign_xor(Q, k.q.y));
+                const f2 off = make_float2(magic_refl(k.q.x), magic_refl(k.q.y));
+#endif
                 const f2    x   = fma2(k.r, sq, off);
                 o[i]            = make_float2(va ? x.x : M, vb ? x.y : M);
             } else {
@@ -344,7 +361,9 @@ constexpr int min_blocks() {
 #else
     if (FEAT == FEAT_MAX_CURVE && SPEC == SPEC_UNIFORM)
         return DC_MC_UNIFORM_BLOCKS;
-    return FEAT == FEAT_CURVATURE ? 3 : 4;  // curvature wants 168 registers (no spills)
+    // curvature wants 168 registers (no spills); bearing fits 128 but measures 3 %
+    // faster with 168 (0.605 -> 0.586 ms per 256 frames of 960x540)
+    return FEAT == FEAT_MAX_CURVE ? 4 : 3;
 #endif
 }
 
@@ -418,34 +437,32 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
     uint4* const  stg2  = smem + 2 * NSLOT * T + threadIdx.x;  // (STAGES == 3 only)
 
     // A stage holds input row r together with the tables of row r-1 (what the
-    // step that consumes row r as its "down" row needs).
-    auto issue_stage = [&](int r, uint4* st) {
+    // step that consumes row r as its "down" row needs). `ro` = r * w.
+    const int  ro_last = (h - 1) * w;
+    auto issue_stage = [&](int r, int ro, uint4* st) {
         const bool in = r < h;
-        issue_raw<R, FC>(L, (in ? r : h - 1) * w, in, st, T);
-        issue_tabs<FEAT, SPEC>(p, r - 1, (r - 1) * w + u0, u0, st + kRawSlots * T, T);
+        issue_raw<R, FC>(L, in ? ro : ro_last, in, st, T);
+        issue_tabs<FEAT, SPEC>(p, r - 1, ro - w + u0, u0, st + kRawSlots * T, T);
     };
-    wrow<FEAT> up, mid, dn;
+    // the three window rows; they rotate by renaming in the three-stage loop
+    wrow<FEAT> w0, w1, w2;
     issue_raw<R, FC>(L, max(v0 - 1, 0) * w, v0 >= 1, stg0, T);
     issue_raw<R, FC>(L, v0 * w, true, stg1, T);
     cp_async_commit();
-    uint4 *sc = stg0, *sf = stg1, *sn = stg1;  // consumed by this step / refilled / consumed next
     if constexpr (STAGES == 3) {
-        issue_stage(v0 + 1, stg2);
+        issue_stage(v0 + 1, (v0 + 1) * w, stg2);
         cp_async_commit();
         cp_async_wait_but_one();
     } else {
         cp_async_wait_all();
     }
-    commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, stg0, T), up);
-    commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, stg1, T), mid);
-    if constexpr (STAGES == 3) {
-        issue_stage(v0 + 2, stg0);
-        cp_async_commit();
-        sc = stg2, sf = stg1, sn = stg0;
-    } else {
-        issue_stage(v0 + 1, stg0);
-        cp_async_commit();
-    }
+    commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, stg0, T), w0);
+    commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, stg1, T), w1);
+    if constexpr (STAGES == 3)
+        issue_stage(v0 + 2, (v0 + 2) * w, stg0);
+    else
+        issue_stage(v0 + 1, (v0 + 1) * w, stg0);
+    cp_async_commit();
 
     pos at;
     at.u0 = u0;
@@ -455,33 +472,9 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
 #pragma unroll
     for (int i = 0; i < 4; ++i)
         col_in[i] = (u0 + i >= 1 && u0 + i < w - 1) ? 1.0f : 0.0f;
-    int cur  = 0;             // (two stages)
-    int roff = (v0 + 1) * w;  // row offset of row v + 1 (two stages)
-#pragma unroll 1
-    for (int v = v0; v < v1; ++v) {
-        rtabs<FEAT> tb;
-        if constexpr (STAGES == 3) {
-            // sc: row v+1 and the tables of row v
-            cp_async_wait_but_one();
-            commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, sc, T), dn);
-            tb = fetch_tabs<FEAT, SPEC>(p, sc + kRawSlots * T, T);
-            issue_stage(v + 3, sf);
-            cp_async_commit();
-            uint4* const consumed = sc;
-            sc = sn, sn = sf, sf = consumed;
-        } else {
-            uint4* const s_now = cur ? stg1 : stg0;  // row v+1 and the tables of row v
-            uint4* const s_nxt = cur ? stg0 : stg1;
-            cur ^= 1;
-            cp_async_wait_all();
-            commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, s_now, T), dn);
-            tb = fetch_tabs<FEAT, SPEC>(p, s_now + kRawSlots * T, T);
-            const bool in2 = v + 2 < h;
-            issue_raw<R, FC>(L, in2 ? roff + w : roff - w, in2, s_nxt, T);
-            issue_tabs<FEAT, SPEC>(p, v + 1, roff + u0, u0, s_nxt + kRawSlots * T, T);
-            cp_async_commit();
-            roff += w;
-        }
+    int  v       = v0;
+    auto do_row = [&](const wrow<FEAT>& up, const wrow<FEAT>& mid, const wrow<FEAT>& dn,
+                      const rtabs<FEAT>& tb) {
         at.v               = v;
         const float row_in = (v >= 1 && v < h - 1) ? 1.0f : 0.0f;
 #pragma unroll
@@ -493,10 +486,298 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
             max_curve_row<OUT>(p, up, mid, dn, tb, at);
         else if constexpr (FEAT == FEAT_CURVATURE)
             curvature_row<OUT, SPEC>(p, up, mid, dn, tb, at, cc);
-        up  = mid;
-        mid = dn;
         at.oa += w;
         at.ob += w;
+    };
+    if constexpr (STAGES == 3) {
+        // Step k = (v - v0) % 3 consumes row v+1 (and the tables of row v) from
+        // stage SC and refills stage SF, consumed one step earlier, with row v+3.
+        // Window rows and stages rotate with the same period, so the loop body is
+        // instantiated three times with the names permuted (no register moves)
+        // where that measured faster, see DC_PAIR_RENAME_MASK.
+        int  ro   = (v0 + 3) * w;  // row offset of row v + 3
+        auto step = [&](const wrow<FEAT>& up, const wrow<FEAT>& mid, wrow<FEAT>& dn, uint4* sc,
+                        uint4* sf) {
+            cp_async_wait_but_one();
+            commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, sc, T), dn);
+            const rtabs<FEAT> tb = fetch_tabs<FEAT, SPEC>(p, sc + kRawSlots * T, T);
+            issue_stage(v + 3, ro, sf);
+            cp_async_commit();
+            ro += w;
+            do_row(up, mid, dn, tb);
+            return ++v < v1;
+        };
+        if constexpr (((DC_PAIR_RENAME_MASK) >> FEAT) & 1) {
+            for (;;) {
+                if (!step(w0, w1, w2, stg2, stg1))
+                    break;
+                if (!step(w1, w2, w0, stg0, stg2))
+                    break;
+                if (!step(w2, w0, w1, stg1, stg0))
+                    break;
+            }
+        } else {
+            uint4 *sc = stg2, *sf = stg1, *sn = stg0;
+#pragma unroll 1
+            for (;;) {
+                const bool more = step(w0, w1, w2, sc, sf);
+                uint4* const consumed = sc;
+                sc = sn, sn = sf, sf = consumed;
+                w0 = w1, w1 = w2;
+                if (!more)
+                    break;
+            }
+        }
+    } else {
+        int cur  = 0;
+        int roff = (v0 + 1) * w;  // row offset of row v + 1
+#pragma unroll 1
+        for (; v < v1; ++v) {
+            uint4* const s_now = cur ? stg1 : stg0;  // row v+1 and the tables of row v
+            uint4* const s_nxt = cur ? stg0 : stg1;
+            cur ^= 1;
+            cp_async_wait_all();
+            commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, s_now, T), w2);
+            const rtabs<FEAT> tb = fetch_tabs<FEAT, SPEC>(p, s_now + kRawSlots * T, T);
+            const bool in2 = v + 2 < h;
+            issue_raw<R, FC>(L, in2 ? roff + w : roff - w, in2, s_nxt, T);
+            issue_tabs<FEAT, SPEC>(p, v + 1, roff + u0, u0, s_nxt + kRawSlots * T, T);
+            cp_async_commit();
+            roff += w;
+            do_row(w0, w1, w2, tb);
+            w0 = w1;
+            w1 = w2;
+        }
+    }
+    cp_async_wait_all();
+}
+
+// ===========================================================================
+// Max-curve with shared edges (conversion/depth_to_max_curve.h:55-153) for
+// cameras whose four neighbour-angle tables are ONE scalar (the clamp of
+// camera_models/utility.h:39-45: Kinect-like intrinsics from 1080p upward).
+//
+// Every pixel pair (X, Y) of the 8-neighbourhood graph is looked along from both
+// ends: bearing_angle(X, Y, c) at pixel X and bearing_angle(Y, X, c) at pixel Y
+// (math/triangles.h:27-64). With the same cosine c at both ends
+//     rad = (XX + YY) - 2 (X Y) c,   den = sqrt(rad),   1 / den
+// are bit-identical for the two calls (sums and products commute), so they are
+// computed once per edge: 9 of the 22 FP32 operations of a bearing angle. Only
+// nom = X - Y c, the quotient and the acos are per end. A step of the row march
+// owns the edges inside row v (horizontal) and from row v down to row v+1
+// (vertical, diagonal, anti-diagonal); the angles at the lower ends are carried
+// to the next step, where they are the "prior" angles of row v+1. The strip's
+// first step runs once without output to produce the carried angles.
+// An invalid edge end (either depth zero, depth_to_max_curve.h:60-61) is carried
+// as a large negative number: it loses every max, and max(., 0) restores the 0.
+struct wrow_sq {
+    f2 r[6];  // range of columns u0-1 .. u0+4, both frames
+    f2 s[6];  // and its square
+};
+struct edge {
+    f2 d, y;  // sqrt(rad), refined reciprocal of it
+    f2 bc;    // X * Y: zero iff either depth is zero
+};
+__device__ __forceinline__ edge edge_shared(f2 x, f2 y, f2 xx, f2 yy, float cu) {
+    edge     e;
+    const f2 sum = add2(xx, yy);
+    e.bc         = mul2(x, y);
+    const f2 t   = mul2(e.bc, B(cu));
+    const f2 rad = fma2(B(-2.0f), t, sum);
+    f2       seed;
+    e.d = sqrt2(rad, seed);
+    e.y = rcp_refine2(e.d, seed);
+    return e;
+}
+#define DC_MC_INVALID (-1.0e30f)
+// bearing angle at pixel x towards pixel y over the shared edge e
+__device__ __forceinline__ f2 edge_end(f2 x, f2 y, const edge& e, float cu) {
+    const f2 nom = sub2(x, mul2(y, B(cu)));
+    const f2 q   = div2(nom, e.d, e.y);
+    const f2 a   = reflect2(acos_abs2(q), q);
+    return make_float2(e.bc.x != 0.0f ? a.x : DC_MC_INVALID, e.bc.y != 0.0f ? a.y : DC_MC_INVALID);
+}
+
+// Register bound: with 128 registers (4 CTAs per SM) ptxas spills 130 bytes and
+// the kernel is SLOWER than pair_kernel<MAX_CURVE> (1.25 vs 1.21 ms on 16 frames
+// of 4096x2160), with 168 it is on par, with 255 (2 CTAs per SM, no spills)
+// 1.06 ms: the 19 edge chains of a step give the scheduler enough independent
+// work from two warps per sub-partition.
+#ifndef DC_MCE_BLOCKS
+#define DC_MCE_BLOCKS 2
+#endif
+constexpr int kMceStages = 3;
+constexpr size_t mce_smem_bytes() { return size_t(kMceStages) * kRawSlots * kPairThreads * sizeof(uint4); }
+
+template <int IN, int OUT>
+__global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
+    maxcurve_edge_kernel(const __grid_constant__ kparams p, int n_frames, int rows_per_strip) {
+    const int       groups_x = p.w >> 2;
+    const int       strips   = (p.h + rows_per_strip - 1) / rows_per_strip;
+    const long long gid      = (long long)blockIdx.x * kPairThreads + threadIdx.x;
+    const int       gx       = int(gid % groups_x);
+    const long long t        = gid / groups_x;
+    const int       pairs    = (n_frames + 1) >> 1;  // pair fastest, see pair_kernel
+    const long long fp       = t % pairs;
+    const int       strip    = int(t / pairs);
+    if (strip >= strips)
+        return;
+    const long long fa = 2 * fp, fb = min(fa + 1, (long long)n_frames - 1);
+    const int  u0 = gx * 4, w = p.w, h = p.h;
+    const int  v0 = strip * rows_per_strip, v1 = min(v0 + rows_per_strip, h);
+    constexpr int FC = IN != IN_U16_DEPTH ? FAC_NONE : FAC_TABLE;
+    lane L;
+    L.A   = static_cast<const unsigned short*>(p.in) + size_t(fa) * p.frame_px + u0;
+    L.Bf  = static_cast<const unsigned short*>(p.in) + size_t(fb) * p.frame_px + u0;
+    L.fac = IN == IN_U16_DEPTH ? p.range_factor.p + u0 : nullptr;
+    L.hl  = u0 > 0;
+    L.hr  = u0 + 4 < w;
+    L.offl = L.hl ? -2 : 0;
+    L.offr = L.hr ? 4 : 0;
+    const float cu = p.cosp[0].value;  // == cosp[1..3].value (checked by the launch code)
+
+    // Three staging stages (dc_pair.cuh "Staging"): `sc` is consumed by this
+    // step, `sn` is in flight for the next one, `sf` was consumed one step ago
+    // and is refilled now: two rows of lead, no barrier.
+    extern __shared__ uint4 smem[];
+    constexpr int T  = kPairThreads;
+    uint4*        sc = smem + threadIdx.x;
+    uint4*        sn = smem + kRawSlots * T + threadIdx.x;
+    uint4*        sf = smem + 2 * kRawSlots * T + threadIdx.x;
+    const int     ro_last = (h - 1) * w;
+    int           rn = v0 + 1, ro = (v0 + 1) * w;  // next row to fetch and its offset
+    auto issue = [&](int r, int roff, uint4* st) {
+        const bool in = r >= 0 && r < h;
+        issue_raw<true, FC>(L, in ? roff : ro_last, in, st, T);
+        cp_async_commit();
+    };
+    auto consume = [&](wrow_sq& dst) {
+        cp_async_wait_but_one();
+        to_range<IN, true>(fetch_raw<true, FC>(L, 1.0f, sc, T), dst.r);
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+            dst.s[i] = mul2(dst.r[i], dst.r[i]);
+        issue(rn, ro, sf);
+        ++rn;
+        ro += w;
+        uint4* const done = sc;
+        sc = sn, sn = sf, sf = done;
+    };
+    issue(v0 - 1, (v0 - 1) * w, sc);
+    issue(v0, v0 * w, sn);
+
+    f2 bv[4], bd[4], ba[4];  // carried: angles at row v towards row v-1 (ver, dia, anti-second)
+    // One step: edges of row `mid` and from `mid` down to `dn`. STORE = false is
+    // the strip prologue (mid = row v0-1): only the carried angles are produced.
+    pos at;
+    at.u0 = u0;
+    at.oa = size_t(fa) * p.frame_px + size_t(v0) * w + u0;
+    at.ob = size_t(fb) * p.frame_px + size_t(v0) * w + u0;
+    float col_in[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        col_in[i] = (u0 + i >= 1 && u0 + i < w - 1) ? 1.0f : 0.0f;
+    int  v    = v0;
+    auto step = [&](const wrow_sq& mid, const wrow_sq& dn, auto store_tag) {
+        constexpr bool STORE = decltype(store_tag)::value;
+        // Direction by direction with a running maximum, the carried angles
+        // replaced in place: few values are live at a time (the kernel is
+        // register bound: 128 registers spill 600 bytes, 255 none).
+        f2 m[4];
+        if constexpr (STORE) {
+            // horizontal edges (j, v) - (j+1, v), j = u0-1 .. u0+3
+            f2 hb = B(0.0f);
+#pragma unroll
+            for (int j = 0; j < 5; ++j) {
+                const edge e = edge_shared(mid.r[j], mid.r[j + 1], mid.s[j], mid.s[j + 1], cu);
+                if (j >= 1)  // pixel j looks right; angle_formula (:55-82): back + forward
+                    m[j - 1] = add2(hb, edge_end(mid.r[j], mid.r[j + 1], e, cu));
+                if (j <= 3)  // pixel j+1 looks left
+                    hb = edge_end(mid.r[j + 1], mid.r[j], e, cu);
+            }
+        }
+        auto take = [&](int i, f2 back, f2 fwd) {
+            const f2 a = add2(back, fwd);
+            m[i]       = make_float2(fmaxf(m[i].x, a.x), fmaxf(m[i].y, a.y));
+        };
+        // vertical edges (c, v) - (c, v+1), columns u0 .. u0+3
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int  c = i + 1;
+            const edge e = edge_shared(mid.r[c], dn.r[c], mid.s[c], dn.s[c], cu);
+            if constexpr (STORE)
+                take(i, bv[i], edge_end(mid.r[c], dn.r[c], e, cu));
+            bv[i] = edge_end(dn.r[c], mid.r[c], e, cu);
+        }
+        // diagonal edges (c, v) - (c+1, v+1), c = u0-1 .. u0+3: pixel c looks
+        // down-right (forward), pixel c+1 of the next row up-left (carried)
+        {
+            f2 pending = B(0.0f);  // the new bd[c-1], stored once the old one is used
+#pragma unroll
+            for (int c = 0; c < 5; ++c) {
+                const edge e = edge_shared(mid.r[c], dn.r[c + 1], mid.s[c], dn.s[c + 1], cu);
+                if (c >= 1) {
+                    if constexpr (STORE)
+                        take(c - 1, bd[c - 1], edge_end(mid.r[c], dn.r[c + 1], e, cu));
+                    bd[c - 1] = pending;
+                }
+                if (c <= 3)
+                    pending = edge_end(dn.r[c + 1], mid.r[c], e, cu);
+            }
+        }
+        // anti-diagonal edges (c, v) - (c-1, v+1), c = u0 .. u0+4: pixel c looks
+        // down-left ("first", :136), pixel c-1 of the next row up-right ("second")
+#pragma unroll
+        for (int c = 1; c < 6; ++c) {
+            const edge e = edge_shared(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], cu);
+            if constexpr (STORE)
+                if (c <= 4)
+                    take(c - 1, ba[c - 1], edge_end(mid.r[c], dn.r[c - 1], e, cu));
+            if (c >= 2)
+                ba[c - 2] = edge_end(dn.r[c - 1], mid.r[c], e, cu);
+        }
+        if constexpr (STORE) {
+            const float row_in = (v >= 1 && v < h - 1) ? 1.0f : 0.0f;
+            f2          o[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                // maximum over the directions (:141-149); invalid ones lose to 0
+                f2 a = make_float2(fmaxf(m[i].x, 0.0f), fmaxf(m[i].y, 0.0f));
+                a    = mul2(a, B(col_in[i] * row_in));  // border stays 0 (:101-102)
+                o[i] = OUT == OUT_U16 ? mul2(a, B(p.q_max_curve)) : a;
+            }
+            store4<OUT>(p.out[0], at.oa, at.ob, o);
+            if (p.out[1] != nullptr) {
+                // the fused `range` output (converter_laserscan.h.inl:9-10)
+                f2 r[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    r[i] = mid.r[i + 1];
+                    if constexpr (OUT == OUT_U16)
+                        r[i] = make_float2(fminf(r[i].x, 65535.0f), fminf(r[i].y, 65535.0f));
+                }
+                store4<OUT>(p.out[1], at.oa, at.ob, r);
+            }
+            at.oa += w;
+            at.ob += w;
+        }
+    };
+
+    // rows alternate between wa and wb (period 2: the loop body is instantiated
+    // twice with the names swapped)
+    wrow_sq wa, wb;
+    consume(wa);  // row v0-1
+    consume(wb);  // row v0
+    step(wa, wb, std::false_type{});
+    for (;;) {
+        consume(wa);  // row v+1
+        step(wb, wa, std::true_type{});
+        if (++v >= v1)
+            break;
+        consume(wb);
+        step(wa, wb, std::true_type{});
+        if (++v >= v1)
+            break;
     }
     cp_async_wait_all();
 }
