@@ -90,6 +90,14 @@ KERNELS = {"bearing": "dc::pr::pair_kernel<FEAT_BEARING, IN_U16_DEPTH, OUT_U16>"
            "range": "dc::pr::stream_kernel<FEAT_RANGE, IN_U16_DEPTH, OUT_U16>"}
 
 
+def kernel_name(feature, wl):
+    """The kernel the library launches for the feature at the workload's frame size."""
+    if feature == "max_curve" and wl["w"] >= 1920:
+        # one scalar neighbour angle (the clamp of camera_models/utility.h:39-45)
+        return "dc::pr::maxcurve_edge_kernel<IN_U16_DEPTH, OUT_U16>"
+    return KERNELS[feature]
+
+
 def ncu_traffic(workload):
     """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the workload's
     kernel, from the committed ncu --set full capture (profiles/r1_traffic.json)."""
@@ -379,8 +387,8 @@ def run_ours(args, wl):
         "gpu_launches": int(launches_timed),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": ncu_traffic(args.workload), "peak_source": peak_src,
-                     "kernel": KERNELS[wl["feature"]] if passes == 1 else
-                     " + ".join(KERNELS[f] for f in [wl["feature"]] + [f for f, _ in extra]),
+                     "kernel": kernel_name(wl["feature"], wl) if passes == 1 else
+                     " + ".join(kernel_name(f, wl) for f in [wl["feature"]] + [f for f, _ in extra]),
                      "launch_ms": avg_kernel_ms,
                      "algorithmic_bytes_per_launch": alg_bytes,
                      "bytes_per_pixel": alg_bytes / (F * px * passes), "passes_per_step": passes},

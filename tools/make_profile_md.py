@@ -10,7 +10,7 @@ out = [f"# Round 1, final kernels ({tag})", "",
        "Box: NVIDIA B200, 16 host vCPUs. Produced by `tools/final_profile.sh` (one gpurun call):",
        "`python bench.py --workload W --steps 20 --warmup 3 --no-cpu-baseline`, the default `python bench.py`,",
        "`python bench.py --impl reference`, an ncu launch list of the default command and one",
-       "`ncu --set full --clock-control none --import-source on -k regex:pair_kernel|stream_kernel -s 1 -c 1`",
+       "`ncu --set full --clock-control none --import-source on -k regex:pair_kernel|stream_kernel|maxcurve_edge_kernel -s 1 -c 1`",
        "capture per workload (second device-resident launch; same grid as the timed launches).", "",
        open(f"{G}/{tag}_pytest_gpu.txt").read().strip().splitlines()[-1] + " (`pytest -m gpu` in the same call)", "",
        "## bench.py (device resident, CUDA events on the launching stream)", "",
