@@ -64,10 +64,27 @@ __device__ __forceinline__ f2 halve2(f2 x) {
 #endif
 }
 
+#ifndef DC_ACOS_MUFU_SQRT
+#define DC_ACOS_MUFU_SQRT 1
+#endif
+#ifndef DC_SQRT_MUFU_SEED
+#define DC_SQRT_MUFU_SEED 0
+#endif
+__device__ __forceinline__ float mufu_sqrt(float x) {
+    float y;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 // RN(sqrt(x)) per half (dc_fastmath.cuh sqrt_rn_fast), y = the rsqrt seed.
 __device__ __forceinline__ f2 sqrt2(f2 x, f2& y) {
     y          = rsq2(x);
+#if DC_SQRT_MUFU_SEED
+    // first estimate from MUFU.SQRT instead of x * rsqrt(x): an XU-pipe slot per
+    // value instead of an FMA-pipe slot per pair (exactness: tests/cuda/mathcheck.cu)
+    f2       g = make_float2(mufu_sqrt(x.x), mufu_sqrt(x.y));
+#else
     f2       g = mul2(x, y);
+#endif
     const f2 h = halve2(y);
     const f2 r = fma2(neg2(g), g, x);
     return fma2(r, h, g);
@@ -92,7 +109,13 @@ __device__ __forceinline__ f2 acos_abs2(f2 q) {
     const f2 a = make_float2(fminf(fabsf(q.x), DC_ONE_MINUS_DELTA),
                              fminf(fabsf(q.y), DC_ONE_MINUS_DELTA));
     const f2 t = sub2(B(1.0f), a);
+#if DC_ACOS_MUFU_SQRT
+    // MUFU.SQRT (max. relative error 2^-23) instead of t * MUFU.RSQ(t): one
+    // FMA-pipe slot less per angle pair, the same two XU-pipe slots
+    const f2 s = make_float2(mufu_sqrt(t.x), mufu_sqrt(t.y));
+#else
     const f2 s = mul2(t, rsq2(t));
+#endif
     f2       p = fma2(B(-0.004307856317609549f), a, B(0.0192753653973341f));
     p          = fma2(p, a, B(-0.044893890619277954f));
     p          = fma2(p, a, B(0.08785323798656464f));

@@ -572,7 +572,9 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
 // as a large negative number: it loses every max, and max(., 0) restores the 0.
 struct wrow_sq {
     f2 r[6];  // range of columns u0-1 .. u0+4, both frames
-    f2 s[6];  // and its square
+    f2 s[6];  // its square
+    f2 c[6];  // and range * cos: with ONE cosine the subtrahend of nom = X - Y c is a
+              // property of pixel Y, shared by the (up to eight) edge ends that look at Y
 };
 struct edge {
     f2 d, y;  // sqrt(rad), refined reciprocal of it
@@ -590,9 +592,9 @@ __device__ __forceinline__ edge edge_shared(f2 x, f2 y, f2 xx, f2 yy, float cu) 
     return e;
 }
 #define DC_MC_INVALID (-1.0e30f)
-// bearing angle at pixel x towards pixel y over the shared edge e
-__device__ __forceinline__ f2 edge_end(f2 x, f2 y, const edge& e, float cu) {
-    const f2 nom = sub2(x, mul2(y, B(cu)));
+// bearing angle at pixel x towards pixel y over the shared edge e; yc = y * cos
+__device__ __forceinline__ f2 edge_end(f2 x, f2 yc, const edge& e) {
+    const f2 nom = sub2(x, yc);
     const f2 q   = div2(nom, e.d, e.y);
     const f2 a   = reflect2(acos_abs2(q), q);
     return make_float2(e.bc.x != 0.0f ? a.x : DC_MC_INVALID, e.bc.y != 0.0f ? a.y : DC_MC_INVALID);
@@ -655,8 +657,10 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
         cp_async_wait_but_one();
         to_range<IN, true>(fetch_raw<true, FC>(L, 1.0f, sc, T), dst.r);
 #pragma unroll
-        for (int i = 0; i < 6; ++i)
+        for (int i = 0; i < 6; ++i) {
             dst.s[i] = mul2(dst.r[i], dst.r[i]);
+            dst.c[i] = mul2(dst.r[i], B(cu));
+        }
         issue(rn, ro, sf);
         ++rn;
         ro += w;
@@ -691,9 +695,9 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
             for (int j = 0; j < 5; ++j) {
                 const edge e = edge_shared(mid.r[j], mid.r[j + 1], mid.s[j], mid.s[j + 1], cu);
                 if (j >= 1)  // pixel j looks right; angle_formula (:55-82): back + forward
-                    m[j - 1] = add2(hb, edge_end(mid.r[j], mid.r[j + 1], e, cu));
+                    m[j - 1] = add2(hb, edge_end(mid.r[j], mid.c[j + 1], e));
                 if (j <= 3)  // pixel j+1 looks left
-                    hb = edge_end(mid.r[j + 1], mid.r[j], e, cu);
+                    hb = edge_end(mid.r[j + 1], mid.c[j], e);
             }
         }
         auto take = [&](int i, f2 back, f2 fwd) {
@@ -706,8 +710,8 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
             const int  c = i + 1;
             const edge e = edge_shared(mid.r[c], dn.r[c], mid.s[c], dn.s[c], cu);
             if constexpr (STORE)
-                take(i, bv[i], edge_end(mid.r[c], dn.r[c], e, cu));
-            bv[i] = edge_end(dn.r[c], mid.r[c], e, cu);
+                take(i, bv[i], edge_end(mid.r[c], dn.c[c], e));
+            bv[i] = edge_end(dn.r[c], mid.c[c], e);
         }
         // diagonal edges (c, v) - (c+1, v+1), c = u0-1 .. u0+3: pixel c looks
         // down-right (forward), pixel c+1 of the next row up-left (carried)
@@ -718,11 +722,11 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
                 const edge e = edge_shared(mid.r[c], dn.r[c + 1], mid.s[c], dn.s[c + 1], cu);
                 if (c >= 1) {
                     if constexpr (STORE)
-                        take(c - 1, bd[c - 1], edge_end(mid.r[c], dn.r[c + 1], e, cu));
+                        take(c - 1, bd[c - 1], edge_end(mid.r[c], dn.c[c + 1], e));
                     bd[c - 1] = pending;
                 }
                 if (c <= 3)
-                    pending = edge_end(dn.r[c + 1], mid.r[c], e, cu);
+                    pending = edge_end(dn.r[c + 1], mid.c[c], e);
             }
         }
         // anti-diagonal edges (c, v) - (c-1, v+1), c = u0 .. u0+4: pixel c looks
@@ -732,9 +736,9 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
             const edge e = edge_shared(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], cu);
             if constexpr (STORE)
                 if (c <= 4)
-                    take(c - 1, ba[c - 1], edge_end(mid.r[c], dn.r[c - 1], e, cu));
+                    take(c - 1, ba[c - 1], edge_end(mid.r[c], dn.c[c - 1], e));
             if (c >= 2)
-                ba[c - 2] = edge_end(dn.r[c - 1], mid.r[c], e, cu);
+                ba[c - 2] = edge_end(dn.r[c - 1], mid.c[c], e);
         }
         if constexpr (STORE) {
             const float row_in = (v >= 1 && v < h - 1) ? 1.0f : 0.0f;

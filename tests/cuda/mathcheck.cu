@@ -3,6 +3,7 @@
 // Prints one line per check: "<name> checked=<n> mismatches=<m> [max_rel=<e>]".
 // Exit code 0 iff every exactness check has 0 mismatches and acos max_rel < 1e-6.
 #include "../../depth-conversions_b200/csrc/dc_fastmath.cuh"
+#include "../../depth-conversions_b200/csrc/dc_pair.cuh"
 
 #include <cmath>
 #include <cstdio>
@@ -55,6 +56,39 @@ __global__ void check_div(unsigned long long* bad, unsigned long long n, int mod
         if (__float_as_uint(dc::div_rn_fast(a, b)) != __float_as_uint(__fdiv_rn(a, b)))
             atomicAdd(bad, 1ull);
     }
+}
+
+// the packed square root of the frame-pair kernels (dc_pair.cuh sqrt2; with
+// -DDC_SQRT_MUFU_SEED=1 its first estimate comes from MUFU.SQRT), exhaustive
+__global__ void check_sqrt_pair(unsigned long long* bad, unsigned lo, unsigned hi) {
+    const unsigned long long n = ((unsigned long long)hi - lo + 2) / 2;
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const unsigned b0 = lo + unsigned(2 * i), b1 = min(b0 + 1, hi);
+        const float2   x  = make_float2(__uint_as_float(b0), __uint_as_float(b1));
+        float2         y;
+        const float2   g = dc::pr::sqrt2(x, y);
+        if (__float_as_uint(g.x) != __float_as_uint(__fsqrt_rn(x.x)))
+            atomicAdd(bad, 1ull);
+        if (__float_as_uint(g.y) != __float_as_uint(__fsqrt_rn(x.y)))
+            atomicAdd(bad, 1ull);
+    }
+}
+// acos of the frame-pair kernels (dc_pair.cuh acos_abs2 + reflect2), exhaustive
+__global__ void check_acos_pair(unsigned long long* worst_bits) {
+    const unsigned hi = __float_as_uint(1.0f);  // acos_abs2 clamps to 1 - 10 eps itself
+    double         w  = 0.0;
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+         i <= hi; i += (unsigned long long)gridDim.x * blockDim.x) {
+        const float  x  = __uint_as_float(unsigned(i));
+        const float2 q  = make_float2(x, -x);
+        const float2 r  = dc::pr::reflect2(dc::pr::acos_abs2(q), q);
+        const float  c  = 1.0f - 10.0f * 1.1920928955078125e-07f;
+        const double xc = double(fminf(x, c));
+        w = fmax(w, fabs(double(r.x) - acos(xc)) / acos(xc));
+        w = fmax(w, fabs(double(r.y) - acos(-xc)) / acos(-xc));
+    }
+    atomicMax(worst_bits, (unsigned long long)__double_as_longlong(w));
 }
 
 // normalisation as flexion does it: component / sqrt(z), reciprocal shared and
@@ -123,6 +157,8 @@ int main() {
     const unsigned lo = 0x0d800000u /* 2^-100 */, hi = 0x7f7fffffu;
     bad += run("sqrt_rn_fast_exhaustive", (unsigned long long)hi - lo + 1,
                [&] { check_sqrt<<<148 * 16, 256>>>(d, lo, hi); });
+    bad += run("pair_sqrt2_exhaustive", (unsigned long long)hi - lo + 1,
+               [&] { check_sqrt_pair<<<148 * 16, 256>>>(d, lo, hi); });
     const unsigned long long N = 1ull << 33;
     for (int m = 0; m < 3; ++m) {
         char nm[64];
@@ -138,7 +174,14 @@ int main() {
     double worst;
     memcpy(&worst, &wb, 8);
     printf("acos_rel exhaustive max_rel=%.3e\n", worst);
-    const bool ok = bad == 0 && worst < 1e-6;
+    cudaMemset(d, 0, 8);
+    check_acos_pair<<<148 * 16, 256>>>(d);
+    cudaDeviceSynchronize();
+    cudaMemcpy(&wb, d, 8, cudaMemcpyDeviceToHost);
+    double worst_pair;
+    memcpy(&worst_pair, &wb, 8);
+    printf("pair acos_abs2 + reflect2 exhaustive max_rel=%.3e\n", worst_pair);
+    const bool ok = bad == 0 && worst < 1e-6 && worst_pair < 2e-6;
     printf("%s\n", ok ? "MATHCHECK OK" : "MATHCHECK FAILED");
     return ok ? 0 : 1;
 }
