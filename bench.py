@@ -83,21 +83,6 @@ def kinect_scaled(w, h):
                 cx=float(f(479.462 * w / 960)), cy=float(f(272.737 * h / 540)))
 
 
-KERNELS = {"bearing": "dc::pr::pair_kernel<FEAT_BEARING, IN_U16_DEPTH, OUT_U16>",
-           "flexion": "dc::pr::flexion_pair_kernel<IN_U16_DEPTH, OUT_U16>",
-           "curvature": "dc::pr::pair_kernel<FEAT_CURVATURE, IN_U16_DEPTH, OUT_F32>",
-           "max_curve": "dc::pr::pair_kernel<FEAT_MAX_CURVE, IN_U16_DEPTH, OUT_U16>",
-           "range": "dc::pr::stream_kernel<FEAT_RANGE, IN_U16_DEPTH, OUT_U16>"}
-
-
-def kernel_name(feature, wl):
-    """The kernel the library launches for the feature at the workload's frame size."""
-    if feature == "max_curve" and wl["w"] >= 1920:
-        # one scalar neighbour angle (the clamp of camera_models/utility.h:39-45)
-        return "dc::pr::maxcurve_edge_kernel<IN_U16_DEPTH, OUT_U16>"
-    return KERNELS[feature]
-
-
 def ncu_traffic(workload):
     """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the workload's
     kernel, from the committed ncu --set full capture (profiles/r1_traffic.json)."""
@@ -283,10 +268,16 @@ def run_ours(args, wl):
     if alg_bytes <= 2 * 126e6:
         flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
+    kernels = []  # kernel family of every pass, as the library reports it (dc_last_kernel)
+
     def launch_all():
         ctx.convert_device(job, sptr)
+        if len(kernels) < passes:
+            kernels.append(ctx.last_kernel)
         for j in more_jobs:
             ctx.convert_device(j, sptr)
+            if len(kernels) < passes:
+                kernels.append(ctx.last_kernel)
 
     def step():
         if flush is not None:
@@ -387,8 +378,8 @@ def run_ours(args, wl):
         "gpu_launches": int(launches_timed),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": ncu_traffic(args.workload), "peak_source": peak_src,
-                     "kernel": kernel_name(wl["feature"], wl) if passes == 1 else
-                     " + ".join(kernel_name(f, wl) for f in [wl["feature"]] + [f for f, _ in extra]),
+                     "kernel": " + ".join(f"{k} [{f}, u16 depth -> {wl['out']}]" for k, f in
+                                          zip(kernels, [wl["feature"]] + [f for f, _ in extra])),
                      "launch_ms": avg_kernel_ms,
                      "algorithmic_bytes_per_launch": alg_bytes,
                      "bytes_per_pixel": alg_bytes / (F * px * passes), "passes_per_step": passes},

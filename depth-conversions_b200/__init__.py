@@ -29,7 +29,7 @@ EXPORTED_SYMBOLS = [
     "dc_version", "dc_device_count", "dc_create", "dc_destroy", "dc_last_error",
     "dc_set_pinhole", "dc_set_equirectangular", "dc_set_frame_size", "dc_width",
     "dc_height", "dc_convert_device", "dc_convert_host", "dc_synchronize",
-    "dc_host_alloc", "dc_host_free", "dc_synth_depth_device", "dc_kernel_launches",
+    "dc_host_alloc", "dc_host_free", "dc_synth_depth_device", "dc_kernel_launches", "dc_last_kernel",
     "dc_quantise_host", "dc_set_pinhole_f64", "dc_set_equirectangular_f64",
     "dc_quantise_host_f64", "dc_median_host", "dc_median_device",
 ]
@@ -95,6 +95,8 @@ def lib():
                                        C.c_void_p, C.c_void_p]
         L.dc_kernel_launches.restype = C.c_uint64
         L.dc_kernel_launches.argtypes = [C.c_void_p]
+        L.dc_last_kernel.restype = C.c_char_p
+        L.dc_last_kernel.argtypes = [C.c_void_p]
         _lib = L
     return _lib
 
@@ -162,6 +164,10 @@ class Context:
     @property
     def kernel_launches(self):
         return int(self._L.dc_kernel_launches(self._h))
+
+    @property
+    def last_kernel(self):
+        return self._L.dc_last_kernel(self._h).decode()
 
     def synchronize(self):
         self._check(self._L.dc_synchronize(self._h))

@@ -63,6 +63,7 @@ struct dc_ctx {
     dev_table    d_range_factor, d_ray[3], d_cos[4], d_curv[3];
     slot         slots[kSlots];
     uint64_t     launches = 0;
+    const char*  last_kernel = "";  // kernel family of the most recent float-path launch
     // Real = double (dc_f64.h): camera parameters in double, tables on demand
     dc64::camera cam64;
     dc64::state* f64 = nullptr;
@@ -272,6 +273,10 @@ int validate_job(dc_ctx* c, const dc_job* j) {
 // ---------------------------------------------------------------------------
 bool aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
 
+// Which kernel family the launch helpers below picked (dc_last_kernel: tests and
+// bench.py name the kernel they measured instead of guessing it).
+thread_local const char* g_kernel = "";
+
 // Rows a thread of the frame-pair kernels marches over (tuning knob:
 // DC_ROWS_PER_STRIP in the environment, read once).
 int rows_per_strip() {
@@ -349,9 +354,13 @@ cudaError_t launch_pair(const dc::kparams& p, int n_frames, cudaStream_t s) {
             const long long eblocks  = (ethreads + dc::pr::kPairThreads - 1) / dc::pr::kPairThreads;
             dc::pr::maxcurve_edge_kernel<IN, OUT>
                 <<<unsigned(eblocks), block, dc::pr::mce_smem_bytes(), s>>>(p, n_frames, edge_rows);
+            g_kernel = "dc::pr::maxcurve_edge_kernel";
             return cudaGetLastError();
         }
     }
+    g_kernel = spec == dc::pr::SPEC_TABLES    ? "dc::pr::pair_kernel<SPEC_TABLES>"
+               : spec == dc::pr::SPEC_UNIFORM ? "dc::pr::pair_kernel<SPEC_UNIFORM>"
+                                              : "dc::pr::pair_kernel<SPEC_GENERIC>";
     switch (spec) {
     case dc::pr::SPEC_TABLES:
         dc::pr::pair_kernel<FEAT, IN, OUT, dc::pr::SPEC_TABLES>
@@ -383,6 +392,7 @@ cudaError_t launch_flexion_pair(const dc::kparams& p, int n_frames, cudaStream_t
     if (carve != cudaSuccess)
         return carve;
     const size_t smem = size_t(3) * dc::pr::kFlexSlots * dc::pr::kPairThreads * sizeof(uint4);
+    g_kernel = "dc::pr::flexion_pair_kernel";
     dc::pr::flexion_pair_kernel<IN, OUT>
         <<<unsigned(blocks), dc::pr::kPairThreads, smem, s>>>(p, n_frames, rps);
     return cudaGetLastError();
@@ -398,6 +408,7 @@ cudaError_t launch_stream(const dc::kparams& p, int n_frames, cudaStream_t s) {
     // about 8 resident blocks per SM; at least 4 frames per thread when possible
     int by = std::max(1, std::min((148 * 8 + bx - 1) / bx, (n_frames + 3) / 4));
     by     = std::min(by, 65535);
+    g_kernel = "dc::pr::stream_kernel";
     dc::pr::stream_kernel<FEAT, IN, OUT><<<dim3(bx, by, 1), 256, 0, s>>>(p, n_frames, groups);
     return cudaGetLastError();
 }
@@ -417,6 +428,7 @@ cudaError_t launch_px(const dc::kparams& p, int n_frames, cudaStream_t s, bool v
         if (vec4 && fast)
             return launch_flexion_pair<IN, OUT>(p, n_frames, s);
     }
+    g_kernel = vec4 && fast ? "dc::feature_kernel<4, fast>" : vec4 ? "dc::feature_kernel<4>" : "dc::feature_kernel<1>";
     const int px = vec4 ? 4 : 1;
     const int qw = (p.w + px - 1) / px;
     // pick the block shape that wastes the fewest threads
@@ -578,6 +590,7 @@ int launch_job(dc_ctx* c, const dc_job* j, cudaStream_t s) {
     if (e != cudaSuccess)
         return cuda_fail(c, e, "kernel launch");
     c->launches += uint64_t((j->n_frames + 65534) / 65535);
+    c->last_kernel = g_kernel;
     return DC_OK;
 }
 
@@ -1089,5 +1102,7 @@ int dc_synth_depth_device(dc_ctx* c, uint64_t seed, int frame0, int n_frames,
 }
 
 uint64_t dc_kernel_launches(const dc_ctx* c) { return c != nullptr ? c->launches : 0; }
+
+const char* dc_last_kernel(const dc_ctx* c) { return c != nullptr ? c->last_kernel : ""; }
 
 }  // extern "C"

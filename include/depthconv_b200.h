@@ -243,6 +243,13 @@ int dc_synth_depth_device(dc_ctx* ctx, uint64_t seed, int frame0, int n_frames,
  * (for the benchmark's gpu_launches claim). */
 uint64_t dc_kernel_launches(const dc_ctx* ctx);
 
+/* Name of the kernel family the most recent dc_convert_* of this context launched
+ * for its (last) chunk, e.g. "dc::pr::maxcurve_edge_kernel"; "" before the first
+ * conversion. The string is static. Test / benchmark introspection: which kernel
+ * serves a job depends on the camera (per-pixel or scalar angle tables), the
+ * input type, the frame width and buffer alignment. */
+const char* dc_last_kernel(const dc_ctx* ctx);
+
 #ifdef __cplusplus
 }
 #endif

@@ -243,3 +243,51 @@ def test_large_batch_properties(pkg, gpu_ctx, oracle):
     assert_u16_parity("flexion", fl[254], oracle.cli_frame(F_FLEXION, 0, base[2], k)[2])
     # border stays 0 (depth_to_flexion.h:156-161)
     assert not fl[:, 0].any() and not fl[:, -1].any() and not fl[:, :, 0].any() and not fl[:, :, -1].any()
+
+
+@pytest.mark.parametrize("w,h,n", [(4, 3, 1), (8, 37, 2), (64, 75, 3), (132, 36, 5), (260, 110, 2)])
+def test_max_curve_shared_edges_small_uniform_cameras(pkg, gpu_ctx, oracle, w, h, n):
+    """maxcurve_edge_kernel (one scalar neighbour angle: telephoto intrinsics clamp
+    every phi() like the 1080p+ Kinect ones, camera_models/utility.h:39-45) at small,
+    ragged sizes: strip seams (36 rows per strip), one thread group per row, odd
+    batches, depth and range input, float and 16-bit output, fused range output."""
+    k = dict(w=w, h=h, fx=2000.0, fy=2010.0, cx=w * 0.49, cy=h * 0.52)
+    set_k(gpu_ctx, k)
+    frames = np.stack([oracle.synth_depth(0xD2C00004, f, w, h) for f in range(n)])
+    frames[0, h // 2, w // 2] = 0  # an invalid pixel inside every neighbourhood kind
+    for in_kind, kind in ((pkg.DC_IN_U16_DEPTH, 0), (pkg.DC_IN_U16_RANGE, 1)):
+        f32 = gpu_ctx.convert(pkg.DC_MAX_CURVE, frames, in_kind, pkg.DC_OUT_F32, want=(True, True))
+        assert gpu_ctx.last_kernel == "dc::pr::maxcurve_edge_kernel", gpu_ctx.last_kernel
+        u16 = gpu_ctx.convert(pkg.DC_MAX_CURVE, frames, in_kind, pkg.DC_OUT_U16, want=(True, True))
+        only = gpu_ctx.convert(pkg.DC_MAX_CURVE, frames, in_kind, pkg.DC_OUT_U16)[0]
+        assert np.array_equal(only, u16[0])
+        for i in range(n):
+            rng = oracle.laserscan(frames[i], k) if kind == 0 else frames[i].astype(np.float32)
+            want = oracle.feature(F_MAX_CURVE, rng, k)
+            assert_float_parity("max_curve", f32[0][i], want)
+            assert_u16_parity("max_curve", u16[0][i], oracle.quantise(F_MAX_CURVE, want, rng))
+            assert_float_parity("range", f32[1][i], rng)
+            assert_u16_parity("range", u16[1][i], oracle.quantise(0, rng, rng))
+            # border stays 0 (depth_to_max_curve.h:101-102)
+            assert not f32[0][i][0].any() and not f32[0][i][-1].any()
+            assert not f32[0][i][:, 0].any() and not f32[0][i][:, -1].any()
+
+
+def test_kernel_selection_is_reported(pkg, gpu_ctx, oracle):
+    """dc_last_kernel: per-pixel angle tables (960x540 Kinect) take the frame-pair
+    kernels with tables, widths that are not a multiple of 4 the scalar kernel."""
+    w, h = 960, 540
+    set_k(gpu_ctx, kinect_scaled(w, h))
+    frames = np.stack([oracle.synth_depth(0xD2C00002, f, w, h) for f in range(2)])
+    gpu_ctx.convert(pkg.DC_BEARING, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16, want=(True,) * 4)
+    assert gpu_ctx.last_kernel == "dc::pr::pair_kernel<SPEC_TABLES>"
+    gpu_ctx.convert(pkg.DC_MAX_CURVE, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)
+    assert gpu_ctx.last_kernel == "dc::pr::pair_kernel<SPEC_TABLES>"
+    gpu_ctx.convert(pkg.DC_FLEXION, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)
+    assert gpu_ctx.last_kernel == "dc::pr::flexion_pair_kernel"
+    gpu_ctx.convert(pkg.DC_RANGE, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)
+    assert gpu_ctx.last_kernel == "dc::pr::stream_kernel"
+    set_k(gpu_ctx, kinect_scaled(322, 203))
+    small = np.stack([oracle.synth_depth(0xD2C00002, 0, 322, 203)])
+    gpu_ctx.convert(pkg.DC_BEARING, small, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16, want=(True,) * 4)
+    assert gpu_ctx.last_kernel.startswith("dc::feature_kernel")
