@@ -334,9 +334,10 @@ cudaError_t launch_pair(const dc::kparams& p, int n_frames, cudaStream_t s) {
     }();
     const int spec = forced == 0 ? 0 : pair_spec<FEAT, IN>(p);
     if constexpr (FEAT == dc::FEAT_MAX_CURVE) {
-        // One scalar for all four neighbour-angle tables (1080p and larger with
-        // Kinect-like intrinsics): the kernel that computes every pixel-pair edge
-        // once for both of its ends (dc_pair_kernels.cuh maxcurve_edge_kernel).
+        // The kernel that computes every pixel-pair edge once for both of its ends
+        // (dc_pair_kernels.cuh maxcurve_edge_kernel): one scalar for all four
+        // neighbour-angle tables (1080p and larger with Kinect-like intrinsics), or
+        // four per-pixel tables (the anti-diagonal pair is not shared there).
         static const int edge_rows = [] {
             const char* e = std::getenv("DC_MCE_ROWS");  // 0 disables the kernel
             return e != nullptr ? std::atoi(e) : 36;
@@ -347,14 +348,30 @@ cudaError_t launch_pair(const dc::kparams& p, int n_frames, cudaStream_t s) {
             return u;
         };
         const unsigned c0 = bits(p.cosp[0].value);
-        if (spec == dc::pr::SPEC_UNIFORM && edge_rows >= 3 && c0 == bits(p.cosp[1].value) &&
-            c0 == bits(p.cosp[2].value) && c0 == bits(p.cosp[3].value)) {
+        const bool one_cos = spec == dc::pr::SPEC_UNIFORM && c0 == bits(p.cosp[1].value) &&
+                             c0 == bits(p.cosp[2].value) && c0 == bits(p.cosp[3].value);
+        if (edge_rows >= 3 && (one_cos || spec == dc::pr::SPEC_TABLES)) {
             const long long estrips  = (p.h + edge_rows - 1) / edge_rows;
             const long long ethreads = pairs * estrips * (p.w / 4);
             const long long eblocks  = (ethreads + dc::pr::kPairThreads - 1) / dc::pr::kPairThreads;
-            dc::pr::maxcurve_edge_kernel<IN, OUT>
-                <<<unsigned(eblocks), block, dc::pr::mce_smem_bytes(), s>>>(p, n_frames, edge_rows);
-            g_kernel = "dc::pr::maxcurve_edge_kernel";
+            if (eblocks > 0x7fffffffLL)
+                return cudaErrorInvalidConfiguration;
+            if (one_cos) {
+                dc::pr::maxcurve_edge_kernel<IN, OUT, dc::pr::SPEC_UNIFORM>
+                    <<<unsigned(eblocks), block, dc::pr::mce_smem_bytes<dc::pr::SPEC_UNIFORM>(), s>>>(
+                        p, n_frames, edge_rows);
+                g_kernel = "dc::pr::maxcurve_edge_kernel<SPEC_UNIFORM>";
+            } else {
+                constexpr size_t smem = dc::pr::mce_smem_bytes<dc::pr::SPEC_TABLES>();  // 54 KB
+                static const cudaError_t attr = cudaFuncSetAttribute(
+                    dc::pr::maxcurve_edge_kernel<IN, OUT, dc::pr::SPEC_TABLES>,
+                    cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+                if (attr != cudaSuccess)
+                    return attr;
+                dc::pr::maxcurve_edge_kernel<IN, OUT, dc::pr::SPEC_TABLES>
+                    <<<unsigned(eblocks), block, smem, s>>>(p, n_frames, edge_rows);
+                g_kernel = "dc::pr::maxcurve_edge_kernel<SPEC_TABLES>";
+            }
             return cudaGetLastError();
         }
     }

@@ -609,11 +609,33 @@ __device__ __forceinline__ f2 edge_end(f2 x, f2 yc, const edge& e) {
 #define DC_MCE_BLOCKS 2
 #endif
 constexpr int kMceStages = 3;
-constexpr size_t mce_smem_bytes() { return size_t(kMceStages) * kRawSlots * kPairThreads * sizeof(uint4); }
+// SPEC_TABLES: per-pixel cosine tables (960x540 Kinect). Per stage, next to the
+// raw slots of input row r:
+//   slot 4: V(r, u0..u0+3)   slot 5: D(r, u0..u0+3)   slot 6: H(r-1, u0..u0+3)
+//   slot 7: A(r-1, u0..u0+3) slot 8: [D(r, u0+4) | H(r-1, u0+4) | A(r-1, u0+4) | -]
+// (X(u, v) = cos(phi((u, v), prior pixel of direction X)), kparams::cosp). The
+// step with rows v (mid) and v+1 = r (down) uses H and A of row v, V and D of row v+1.
+template <int SPEC>
+__host__ __device__ constexpr int mce_slots() {
+    return kRawSlots + (SPEC == SPEC_TABLES ? 5 : 0);
+}
+template <int SPEC>
+constexpr size_t mce_smem_bytes() {
+    return size_t(kMceStages) * mce_slots<SPEC>() * kPairThreads * sizeof(uint4);
+}
+// cosines of one step; SPEC_UNIFORM: every entry is the one scalar
+struct mce_cos {
+    float h[5];  // horizontal edge j = (u0-1+j, v) - (u0+j, v):        H(u0+j, v)
+    float v[4];  // vertical edge of column u0+i:                       V(u0+i, v+1)
+    float d[5];  // diagonal edge (u0-1+c, v) - (u0+c, v+1):            D(u0+c, v+1)
+    float a[4];  // anti-diagonal, seen from (u0+i, v+1) ("second"):    A(u0+i+1, v)
+};
 
-template <int IN, int OUT>
+template <int IN, int OUT, int SPEC>
 __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
     maxcurve_edge_kernel(const __grid_constant__ kparams p, int n_frames, int rows_per_strip) {
+    static_assert(SPEC == SPEC_UNIFORM || SPEC == SPEC_TABLES, "");
+    constexpr bool TAB = SPEC == SPEC_TABLES;
     const int       groups_x = p.w >> 2;
     const int       strips   = (p.h + rows_per_strip - 1) / rows_per_strip;
     const long long gid      = (long long)blockIdx.x * kPairThreads + threadIdx.x;
@@ -636,30 +658,58 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
     L.hr  = u0 + 4 < w;
     L.offl = L.hl ? -2 : 0;
     L.offr = L.hr ? 4 : 0;
-    const float cu = p.cosp[0].value;  // == cosp[1..3].value (checked by the launch code)
+    const float cu = p.cosp[0].value;  // SPEC_UNIFORM: == cosp[1..3].value (checked by the launch code)
 
     // Three staging stages (dc_pair.cuh "Staging"): `sc` is consumed by this
     // step, `sn` is in flight for the next one, `sf` was consumed one step ago
     // and is refilled now: two rows of lead, no barrier.
     extern __shared__ uint4 smem[];
     constexpr int T  = kPairThreads;
+    constexpr int NS = mce_slots<SPEC>();
     uint4*        sc = smem + threadIdx.x;
-    uint4*        sn = smem + kRawSlots * T + threadIdx.x;
-    uint4*        sf = smem + 2 * kRawSlots * T + threadIdx.x;
+    uint4*        sn = smem + NS * T + threadIdx.x;
+    uint4*        sf = smem + 2 * NS * T + threadIdx.x;
     const int     ro_last = (h - 1) * w;
     int           rn = v0 + 1, ro = (v0 + 1) * w;  // next row to fetch and its offset
     auto issue = [&](int r, int roff, uint4* st) {
         const bool in = r >= 0 && r < h;
         issue_raw<true, FC>(L, in ? roff : ro_last, in, st, T);
+        if constexpr (TAB) {
+            // tables of row r (V, D) and of row r-1 (H, A); entries of pixels whose
+            // prior neighbour lies outside the image are never used unmasked
+            const bool in1 = r >= 1 && r <= h, more = u0 + 4 < w;
+            const int  o0 = (in ? roff : ro_last) + u0, o1 = (in1 ? roff - w : 0) + u0;
+            const int  o4 = more ? 4 : 0;
+            cp_async<16>(st + 4 * T, p.cosp[1].p + o0, in);
+            cp_async<16>(st + 5 * T, p.cosp[2].p + o0, in);
+            cp_async<16>(st + 6 * T, p.cosp[0].p + o1, in1);
+            cp_async<16>(st + 7 * T, p.cosp[3].p + o1, in1);
+            char* e = reinterpret_cast<char*>(st + 8 * T);
+            cp_async<4>(e, p.cosp[2].p + o0 + o4, in && more);
+            cp_async<4>(e + 4, p.cosp[0].p + o1 + o4, in1 && more);
+            cp_async<4>(e + 8, p.cosp[3].p + o1 + o4, in1 && more);
+        }
         cp_async_commit();
     };
-    auto consume = [&](wrow_sq& dst) {
+    auto consume = [&](wrow_sq& dst, mce_cos& cs) {
         cp_async_wait_but_one();
         to_range<IN, true>(fetch_raw<true, FC>(L, 1.0f, sc, T), dst.r);
 #pragma unroll
         for (int i = 0; i < 6; ++i) {
             dst.s[i] = mul2(dst.r[i], dst.r[i]);
-            dst.c[i] = mul2(dst.r[i], B(cu));
+            if constexpr (!TAB)
+                dst.c[i] = mul2(dst.r[i], B(cu));
+        }
+        if constexpr (TAB) {
+            const float4 tv = *reinterpret_cast<const float4*>(sc + 4 * T);
+            const float4 td = *reinterpret_cast<const float4*>(sc + 5 * T);
+            const float4 th = *reinterpret_cast<const float4*>(sc + 6 * T);
+            const float4 ta = *reinterpret_cast<const float4*>(sc + 7 * T);
+            const float4 te = *reinterpret_cast<const float4*>(sc + 8 * T);
+            cs.v[0] = tv.x, cs.v[1] = tv.y, cs.v[2] = tv.z, cs.v[3] = tv.w;
+            cs.d[0] = td.x, cs.d[1] = td.y, cs.d[2] = td.z, cs.d[3] = td.w, cs.d[4] = te.x;
+            cs.h[0] = th.x, cs.h[1] = th.y, cs.h[2] = th.z, cs.h[3] = th.w, cs.h[4] = te.y;
+            cs.a[0] = ta.y, cs.a[1] = ta.z, cs.a[2] = ta.w, cs.a[3] = te.z;
         }
         issue(rn, ro, sf);
         ++rn;
@@ -682,8 +732,16 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
     for (int i = 0; i < 4; ++i)
         col_in[i] = (u0 + i >= 1 && u0 + i < w - 1) ? 1.0f : 0.0f;
     int  v    = v0;
-    auto step = [&](const wrow_sq& mid, const wrow_sq& dn, auto store_tag) {
+    auto step = [&](const wrow_sq& mid, const wrow_sq& dn, const mce_cos& cs, auto store_tag) {
         constexpr bool STORE = decltype(store_tag)::value;
+        // y * cos for the end that looks at y: shared per pixel with one cosine
+        auto yc = [&](const wrow_sq& row, int i, float c) {
+            if constexpr (TAB)
+                return mul2(row.r[i], B(c));
+            else
+                return row.c[i];
+        };
+        auto cs_ = [&](float c) { return TAB ? c : cu; };
         // Direction by direction with a running maximum, the carried angles
         // replaced in place: few values are live at a time (the kernel is
         // register bound: 128 registers spill 600 bytes, 255 none).
@@ -693,11 +751,12 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
             f2 hb = B(0.0f);
 #pragma unroll
             for (int j = 0; j < 5; ++j) {
-                const edge e = edge_shared(mid.r[j], mid.r[j + 1], mid.s[j], mid.s[j + 1], cu);
+                const float c = cs_(cs.h[j]);
+                const edge  e = edge_shared(mid.r[j], mid.r[j + 1], mid.s[j], mid.s[j + 1], c);
                 if (j >= 1)  // pixel j looks right; angle_formula (:55-82): back + forward
-                    m[j - 1] = add2(hb, edge_end(mid.r[j], mid.c[j + 1], e));
+                    m[j - 1] = add2(hb, edge_end(mid.r[j], yc(mid, j + 1, c), e));
                 if (j <= 3)  // pixel j+1 looks left
-                    hb = edge_end(mid.r[j + 1], mid.c[j], e);
+                    hb = edge_end(mid.r[j + 1], yc(mid, j, c), e);
             }
         }
         auto take = [&](int i, f2 back, f2 fwd) {
@@ -707,11 +766,12 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
         // vertical edges (c, v) - (c, v+1), columns u0 .. u0+3
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const int  c = i + 1;
-            const edge e = edge_shared(mid.r[c], dn.r[c], mid.s[c], dn.s[c], cu);
+            const int   c  = i + 1;
+            const float co = cs_(cs.v[i]);
+            const edge  e  = edge_shared(mid.r[c], dn.r[c], mid.s[c], dn.s[c], co);
             if constexpr (STORE)
-                take(i, bv[i], edge_end(mid.r[c], dn.c[c], e));
-            bv[i] = edge_end(dn.r[c], mid.c[c], e);
+                take(i, bv[i], edge_end(mid.r[c], yc(dn, c, co), e));
+            bv[i] = edge_end(dn.r[c], yc(mid, c, co), e);
         }
         // diagonal edges (c, v) - (c+1, v+1), c = u0-1 .. u0+3: pixel c looks
         // down-right (forward), pixel c+1 of the next row up-left (carried)
@@ -719,26 +779,43 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
             f2 pending = B(0.0f);  // the new bd[c-1], stored once the old one is used
 #pragma unroll
             for (int c = 0; c < 5; ++c) {
-                const edge e = edge_shared(mid.r[c], dn.r[c + 1], mid.s[c], dn.s[c + 1], cu);
+                const float co = cs_(cs.d[c]);
+                const edge  e  = edge_shared(mid.r[c], dn.r[c + 1], mid.s[c], dn.s[c + 1], co);
                 if (c >= 1) {
                     if constexpr (STORE)
-                        take(c - 1, bd[c - 1], edge_end(mid.r[c], dn.c[c + 1], e));
+                        take(c - 1, bd[c - 1], edge_end(mid.r[c], yc(dn, c + 1, co), e));
                     bd[c - 1] = pending;
                 }
                 if (c <= 3)
-                    pending = edge_end(dn.r[c + 1], mid.c[c], e);
+                    pending = edge_end(dn.r[c + 1], yc(mid, c, co), e);
             }
         }
         // anti-diagonal edges (c, v) - (c-1, v+1), c = u0 .. u0+4: pixel c looks
-        // down-left ("first", :136), pixel c-1 of the next row up-right ("second")
+        // down-left ("first": with the cosine of ITS diagonal successor, sic :136),
+        // pixel c-1 of the next row up-right ("second", A(c, v)). Two cosines with
+        // per-pixel tables: nothing to share there.
 #pragma unroll
         for (int c = 1; c < 6; ++c) {
-            const edge e = edge_shared(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], cu);
-            if constexpr (STORE)
-                if (c <= 4)
-                    take(c - 1, ba[c - 1], edge_end(mid.r[c], dn.c[c - 1], e));
-            if (c >= 2)
-                ba[c - 2] = edge_end(dn.r[c - 1], mid.c[c], e);
+            if constexpr (!TAB) {
+                const edge e = edge_shared(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], cu);
+                if constexpr (STORE)
+                    if (c <= 4)
+                        take(c - 1, ba[c - 1], edge_end(mid.r[c], dn.c[c - 1], e));
+                if (c >= 2)
+                    ba[c - 2] = edge_end(dn.r[c - 1], mid.c[c], e);
+            } else {
+                if constexpr (STORE)
+                    if (c <= 4) {
+                        const float co = cs.d[c];  // D(u + 1, v + 1), u = u0 + c - 1
+                        const edge  e  = edge_shared(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], co);
+                        take(c - 1, ba[c - 1], edge_end(mid.r[c], mul2(dn.r[c - 1], B(co)), e));
+                    }
+                if (c >= 2) {
+                    const float co = cs.a[c - 2];  // A(u0 + c - 1, v)
+                    const edge  e  = edge_shared(dn.r[c - 1], mid.r[c], dn.s[c - 1], mid.s[c], co);
+                    ba[c - 2]      = edge_end(dn.r[c - 1], mul2(mid.r[c], B(co)), e);
+                }
+            }
         }
         if constexpr (STORE) {
             const float row_in = (v >= 1 && v < h - 1) ? 1.0f : 0.0f;
@@ -770,16 +847,17 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
     // rows alternate between wa and wb (period 2: the loop body is instantiated
     // twice with the names swapped)
     wrow_sq wa, wb;
-    consume(wa);  // row v0-1
-    consume(wb);  // row v0
-    step(wa, wb, std::false_type{});
+    mce_cos cs;
+    consume(wa, cs);  // row v0-1
+    consume(wb, cs);  // row v0 (+ the tables of the step rows v0-1 / v0)
+    step(wa, wb, cs, std::false_type{});
     for (;;) {
-        consume(wa);  // row v+1
-        step(wb, wa, std::true_type{});
+        consume(wa, cs);  // row v+1
+        step(wb, wa, cs, std::true_type{});
         if (++v >= v1)
             break;
-        consume(wb);
-        step(wa, wb, std::true_type{});
+        consume(wb, cs);
+        step(wa, wb, cs, std::true_type{});
         if (++v >= v1)
             break;
     }

@@ -257,7 +257,7 @@ def test_max_curve_shared_edges_small_uniform_cameras(pkg, gpu_ctx, oracle, w, h
     frames[0, h // 2, w // 2] = 0  # an invalid pixel inside every neighbourhood kind
     for in_kind, kind in ((pkg.DC_IN_U16_DEPTH, 0), (pkg.DC_IN_U16_RANGE, 1)):
         f32 = gpu_ctx.convert(pkg.DC_MAX_CURVE, frames, in_kind, pkg.DC_OUT_F32, want=(True, True))
-        assert gpu_ctx.last_kernel == "dc::pr::maxcurve_edge_kernel", gpu_ctx.last_kernel
+        assert gpu_ctx.last_kernel == "dc::pr::maxcurve_edge_kernel<SPEC_UNIFORM>", gpu_ctx.last_kernel
         u16 = gpu_ctx.convert(pkg.DC_MAX_CURVE, frames, in_kind, pkg.DC_OUT_U16, want=(True, True))
         only = gpu_ctx.convert(pkg.DC_MAX_CURVE, frames, in_kind, pkg.DC_OUT_U16)[0]
         assert np.array_equal(only, u16[0])
@@ -282,7 +282,7 @@ def test_kernel_selection_is_reported(pkg, gpu_ctx, oracle):
     gpu_ctx.convert(pkg.DC_BEARING, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16, want=(True,) * 4)
     assert gpu_ctx.last_kernel == "dc::pr::pair_kernel<SPEC_TABLES>"
     gpu_ctx.convert(pkg.DC_MAX_CURVE, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)
-    assert gpu_ctx.last_kernel == "dc::pr::pair_kernel<SPEC_TABLES>"
+    assert gpu_ctx.last_kernel == "dc::pr::maxcurve_edge_kernel<SPEC_TABLES>"
     gpu_ctx.convert(pkg.DC_FLEXION, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)
     assert gpu_ctx.last_kernel == "dc::pr::flexion_pair_kernel"
     gpu_ctx.convert(pkg.DC_RANGE, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)
