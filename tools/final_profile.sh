@@ -12,7 +12,7 @@ python bench.py > gpurun_out/${TAG}_bench_default.json 2> gpurun_out/${TAG}_benc
 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${TAG}_bench_ref.json 2> gpurun_out/${TAG}_bench_ref.err
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches_bearing4.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/${TAG}_ncu_launches.log 2>&1
-for wl in bearing4_960x540 flexion_960x540 curvature_1920x1080 range_maxcurve_4096x2160 range_960x540; do
+for wl in bearing4_960x540 flexion_960x540 curvature_1920x1080 range_maxcurve_4096x2160 maxcurve_960x540 range_960x540; do
   ncu --set full --clock-control none --import-source on -k 'regex:pair_kernel|stream_kernel|maxcurve_edge_kernel' -s 1 -c 1 -f -o gpurun_out/${TAG}_ncu_$wl \
       python bench.py --workload $wl --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/${TAG}_ncu_$wl.log 2>&1
   # gpurun_out travels back only below 64 MiB: keep the CSV pages, drop the report

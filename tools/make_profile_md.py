@@ -37,7 +37,7 @@ want = ['Kernel Name', 'Block Size', 'Grid Size', 'gpu__time_duration.sum', 'dra
         'lts__t_sector_hit_rate.pct', 'lts__throughput.avg.pct_of_peak_sustained_elapsed']
 out.append("## ncu --set full (one launch each)")
 traffic = {}
-for wl in ["bearing4_960x540", "flexion_960x540", "curvature_1920x1080", "range_maxcurve_4096x2160", "range_960x540"]:
+for wl in ["bearing4_960x540", "flexion_960x540", "curvature_1920x1080", "range_maxcurve_4096x2160", "maxcurve_960x540", "range_960x540"]:
     rows = list(csv.reader(io.StringIO(open(f"{G}/{tag}_ncu_{wl}_raw.csv").read())))
     hdr, units, vals = rows[0], rows[1], rows[2]
     def get(k):
