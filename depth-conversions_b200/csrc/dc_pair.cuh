@@ -70,6 +70,9 @@ __device__ __forceinline__ f2 halve2(f2 x) {
 #ifndef DC_SQRT_MUFU_SEED
 #define DC_SQRT_MUFU_SEED 0
 #endif
+#ifndef DC_APPROX_RATIO
+#define DC_APPROX_RATIO 0
+#endif
 __device__ __forceinline__ float mufu_sqrt(float x) {
     float y;
     asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -163,9 +166,16 @@ __device__ __forceinline__ bres bearing_core2(f2 b, f2 c, f2 bb, f2 cc, float co
     o.bc         = mul2(b, c);
     const f2 t   = mul2(o.bc, ca);
     const f2 rad = fma2(B(-2.0f), t, sum);
+#if DC_APPROX_RATIO
+    // EXPERIMENT ONLY (profiles/r1_ab_experiments.md section 7): the ratio as
+    // nom * rsqrt(rad), 1 FFMA2 instead of 8. Not the reference's
+    // RN(nom / RN(sqrt(rad))): fails the 1e-5 contract where acos is steep.
+    o.q = mul2(nom, rsq2(rad));
+#else
     f2       y;
     const f2 d = sqrt2(rad, y);
     o.q        = div2(nom, d, rcp_refine2(d, y));
+#endif
     o.r        = acos_abs2(o.q);
     return o;
 }
