@@ -126,7 +126,65 @@ __device__ __forceinline__ f2 acos_abs2(f2 q) {
     p          = fma2(p, a, B(1.5707951784133911f));
     return mul2(s, p);
 }
+// The two factors separately, the polynomial with its coefficients pre-multiplied
+// by a scale K (k[i] = K * coefficient i, lowest first): acos(min(|q|, 1 - delta)) * K
+// = s * pk. The u16 bearing epilogue folds s * pk into its final FFMA2 and saves
+// the product (one FMA-pipe slot per angle pair).
+struct acos_scaled {
+    float k[6];
+};
+__device__ __forceinline__ acos_scaled acos_scale(float K) {
+    acos_scaled c;
+    c.k[0] = __fmul_rn(K, 1.5707951784133911f);
+    c.k[1] = __fmul_rn(K, -0.2145095020532608f);
+    c.k[2] = __fmul_rn(K, 0.08785323798656464f);
+    c.k[3] = __fmul_rn(K, -0.044893890619277954f);
+    c.k[4] = __fmul_rn(K, 0.0192753653973341f);
+    c.k[5] = __fmul_rn(K, -0.004307856317609549f);
+    return c;
+}
+__device__ __forceinline__ void acos_parts2(f2 q, const acos_scaled& c, f2& s, f2& pk) {
+    const f2 a = make_float2(fminf(fabsf(q.x), DC_ONE_MINUS_DELTA),
+                             fminf(fabsf(q.y), DC_ONE_MINUS_DELTA));
+    const f2 t = sub2(B(1.0f), a);
+    s          = make_float2(mufu_sqrt(t.x), mufu_sqrt(t.y));
+    pk         = fma2(B(c.k[5]), a, B(c.k[4]));
+    pk         = fma2(pk, a, B(c.k[3]));
+    pk         = fma2(pk, a, B(c.k[2]));
+    pk         = fma2(pk, a, B(c.k[1]));
+    pk         = fma2(pk, a, B(c.k[0]));
+}
 #define DC_PI_F 3.14159274101257324f
+// acos(clamp(q, -1 + delta, 1 - delta)), what the kernels call.
+// DC_ACOS_FOLD_REFLECT=1 puts the reflection inside the last FFMA2 (q < 0:
+// pi - s p = fma(-s, p, pi), else fma(s, p, 0)): one packed instruction less per
+// angle pair, but an FFMA2 with three distinct register operands costs 3.1 clocks
+// against 2 x 2.07 with an immediate each, and measured SLOWER (max-curve 960x540
+// 1.054 -> 1.122 ms, profiles/r1_ab_experiments.md section 8). Off.
+#ifndef DC_ACOS_FOLD_REFLECT
+#define DC_ACOS_FOLD_REFLECT 0
+#endif
+__device__ __forceinline__ f2 acos_signed2(f2 q) {
+    const f2 a = make_float2(fminf(fabsf(q.x), DC_ONE_MINUS_DELTA),
+                             fminf(fabsf(q.y), DC_ONE_MINUS_DELTA));
+    const f2 t = sub2(B(1.0f), a);
+    const f2 s = make_float2(mufu_sqrt(t.x), mufu_sqrt(t.y));
+    f2       p = fma2(B(-0.004307856317609549f), a, B(0.0192753653973341f));
+    p          = fma2(p, a, B(-0.044893890619277954f));
+    p          = fma2(p, a, B(0.08785323798656464f));
+    p          = fma2(p, a, B(-0.2145095020532608f));
+    p          = fma2(p, a, B(1.5707951784133911f));
+#if DC_ACOS_FOLD_REFLECT
+    const bool na = q.x < 0.0f, nb = q.y < 0.0f;
+    const f2   ss  = make_float2(na ? -s.x : s.x, nb ? -s.y : s.y);
+    const f2   off = make_float2(na ? DC_PI_F : 0.0f, nb ? DC_PI_F : 0.0f);
+    return fma2(ss, p, off);
+#else
+    const f2 r = mul2(s, p);
+    const f2 m = sub2(B(DC_PI_F), r);
+    return make_float2(q.x < 0.0f ? m.x : r.x, q.y < 0.0f ? m.y : r.y);
+#endif
+}
 // u16 reflection without compares (bearing epilogue; DC_REFLECT_FSEL=0, measured
 // 1.5 % slower than the compare + select form, see halve2): for the ratio q
 //   sign_xor(Q, q)  = q < 0 ? -Q : Q             (one LOP3)
@@ -158,6 +216,7 @@ struct bres {
     f2 q;   // the ratio: its sign selects the reflection
     f2 bc;  // b * c
 };
+template <bool WITH_ACOS = true>
 __device__ __forceinline__ bres bearing_core2(f2 b, f2 c, f2 bb, f2 cc, float cos_alpha) {
     bres     o;
     const f2 ca  = B(cos_alpha);
@@ -176,7 +235,8 @@ __device__ __forceinline__ bres bearing_core2(f2 b, f2 c, f2 bb, f2 cc, float co
     const f2 d = sqrt2(rad, y);
     o.q        = div2(nom, d, rcp_refine2(d, y));
 #endif
-    o.r        = acos_abs2(o.q);
+    if constexpr (WITH_ACOS)
+        o.r = acos_abs2(o.q);
     return o;
 }
 

@@ -13,6 +13,13 @@ constexpr int kPairThreads = 128;
 #ifndef DC_REFLECT_FSEL
 #define DC_REFLECT_FSEL 1
 #endif
+// 1: the u16 bearing epilogue multiplies the acos polynomial's coefficients by
+// 65535/pi and folds s * (Q P) into the rounding FFMA2 (16 FFMA2 per row less).
+// Measured no faster (0.5723 vs 0.5704 ms): the scaled coefficients are register
+// operands instead of immediates. Off.
+#ifndef DC_BEARING_FOLD_Q
+#define DC_BEARING_FOLD_Q 0
+#endif
 // Features whose three-stage row loop is instantiated three times with the
 // window rows / stages renamed instead of rotated (bit mask over FEAT_*).
 // Measured: curvature 0.443 -> 0.429 ms, bearing 0.605 -> 0.615 ms (kept rotating).
@@ -150,6 +157,7 @@ __device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BE
                                             const wrow<FEAT_BEARING>& mid,
                                             const wrow<FEAT_BEARING>& dn,
                                             const rtabs<FEAT_BEARING>& tb, const pos& at) {
+    [[maybe_unused]] const acos_scaled aq = acos_scale(p.q_bearing);
     f2 sm[5];  // squares of the centre row: b*b of every pixel, c*c for horizontal
 #pragma unroll
     for (int i = 0; i < 5; ++i)
@@ -166,7 +174,8 @@ __device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BE
             // prior pixel: hor (u-1,v), ver (u,v-1), dia (u-1,v-1), anti (u-1,v+1)
             const f2   c  = d == 0 ? mid.r[i] : d == 1 ? up.r[i + 1] : d == 2 ? up.r[i] : dn.r[i];
             const f2   cc = d == 0 ? sm[i] : mul2(c, c);
-            const bres k  = bearing_core2(b, c, bb, cc, cs[i]);
+            constexpr bool WITH_ACOS = OUT == OUT_U16 && !DC_BEARING_FOLD_Q;
+            const bres k  = bearing_core2<WITH_ACOS>(b, c, bb, cc, cs[i]);
             // depth_to_bearing.h:204-207: either depth 0 (or the prior pixel
             // outside the image, which reads as 0) -> 0
             const bool va = k.bc.x != 0.0f, vb = k.bc.y != 0.0f;
@@ -178,6 +187,18 @@ __device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BE
                 // (tolerance of the quantised images: +-1 LSB; acos itself is
                 // only 1e-6 accurate against glibc).
                 const float Q = p.q_bearing, M = 12582912.0f;
+#if DC_BEARING_FOLD_Q
+                // acos = s * P(a): the scale goes into the polynomial's coefficients
+                // (loop invariant), the reflection's sign onto s, and the product
+                // s * (Q P) happens inside the rounding FFMA2.
+                const float C  = fmaf(DC_PI_F, Q, M);
+                const bool  na = k.q.x < 0.0f, nb = k.q.y < 0.0f;
+                f2          s, pk;
+                acos_parts2(k.q, aq, s, pk);
+                const f2 ss  = make_float2(na ? -s.x : s.x, nb ? -s.y : s.y);
+                const f2 off = make_float2(na ? C : M, nb ? C : M);
+                const f2 x   = fma2(ss, pk, off);
+#else
 #if DC_REFLECT_FSEL
                 const float C  = fmaf(DC_PI_F, Q, M);
                 const bool  na = k.q.x < 0.0f, nb = k.q.y < 0.0f;
@@ -188,9 +209,10 @@ __device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BE
                 const f2 off = make_float2(magic_refl(k.q.x), magic_refl(k.q.y));
 #endif
                 const f2    x   = fma2(k.r, sq, off);
+#endif
                 o[i]            = make_float2(va ? x.x : M, vb ? x.y : M);
             } else {
-                const f2 a = reflect2(k.r, k.q);
+                const f2 a = acos_signed2(k.q);
                 o[i]       = make_float2(va ? a.x : 0.0f, vb ? a.y : 0.0f);
             }
         }
@@ -222,9 +244,9 @@ __device__ __forceinline__ void max_curve_row(const kparams& p, const wrow<FEAT_
         // angle_formula (:55-82): 0 if any of the three depths is 0, else the
         // sum of the two bearing angles
         auto pair = [&](f2 dm, f2 smm, f2 dp, f2 spp, float c1, float c2) {
-            const bres k1 = bearing_core2(d0, dm, bb, smm, c1);
-            const bres k2 = bearing_core2(d0, dp, bb, spp, c2);
-            const f2   s  = add2(reflect2(k1.r, k1.q), reflect2(k2.r, k2.q));
+            const bres k1 = bearing_core2<false>(d0, dm, bb, smm, c1);
+            const bres k2 = bearing_core2<false>(d0, dp, bb, spp, c2);
+            const f2   s  = add2(acos_signed2(k1.q), acos_signed2(k2.q));
             return make_float2((k1.bc.x != 0.0f && k2.bc.x != 0.0f) ? s.x : 0.0f,
                                (k1.bc.y != 0.0f && k2.bc.y != 0.0f) ? s.y : 0.0f);
         };
@@ -596,7 +618,7 @@ __device__ __forceinline__ edge edge_shared(f2 x, f2 y, f2 xx, f2 yy, float cu) 
 __device__ __forceinline__ f2 edge_end(f2 x, f2 yc, const edge& e) {
     const f2 nom = sub2(x, yc);
     const f2 q   = div2(nom, e.d, e.y);
-    const f2 a   = reflect2(acos_abs2(q), q);
+    const f2 a   = acos_signed2(q);
     return make_float2(e.bc.x != 0.0f ? a.x : DC_MC_INVALID, e.bc.y != 0.0f ? a.y : DC_MC_INVALID);
 }
 
