@@ -363,7 +363,9 @@ cudaError_t launch_pair(const dc::kparams& p, int n_frames, cudaStream_t s) {
                 g_kernel = "dc::pr::maxcurve_edge_kernel<SPEC_UNIFORM>";
             } else {
                 constexpr size_t smem = dc::pr::mce_smem_bytes<dc::pr::SPEC_TABLES>();  // 54 KB
-                static const cudaError_t attr = cudaFuncSetAttribute(
+                // per device, hence not cached in a static (depth2x --devices N runs
+                // one context per GPU in one process); a few microseconds per launch
+                const cudaError_t attr = cudaFuncSetAttribute(
                     dc::pr::maxcurve_edge_kernel<IN, OUT, dc::pr::SPEC_TABLES>,
                     cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
                 if (attr != cudaSuccess)
@@ -410,7 +412,8 @@ cudaError_t launch_flexion_pair(const dc::kparams& p, int n_frames, cudaStream_t
     const long long blocks  = (threads + dc::pr::kPairThreads - 1) / dc::pr::kPairThreads;
     if (blocks > 0x7fffffffLL)
         return cudaErrorInvalidConfiguration;
-    static const cudaError_t carve = cudaFuncSetAttribute(
+    // per device (one context per GPU in a depth2x --devices N process): not cached
+    const cudaError_t carve = cudaFuncSetAttribute(
         dc::pr::flexion_pair_kernel<IN, OUT>, cudaFuncAttributePreferredSharedMemoryCarveout,
         int(cudaSharedmemCarveoutMaxShared));
     if (carve != cudaSuccess)

@@ -198,3 +198,19 @@ def test_cpp_library_api(tmp_path, oracle):
     assert np.array_equal(cv2.imread(str(tmp_path / "median5.png"), cv2.IMREAD_UNCHANGED),
                           cv2.medianBlur(depth, 5))
     assert np.array_equal(f32("median3"), cv2.medianBlur(f32("range"), 3))
+
+
+def test_devices_sharding_in_one_process(scene, oracle, pkg):
+    """depth2x --devices 2: one context per GPU in ONE process, frames sharded by
+    index. max-curve and flexion at 960x540 take kernels that need
+    per-device function attributes (54 KB of dynamic shared memory). Needs two GPUs."""
+    if pkg.lib().dc_device_count() < 2:
+        pytest.skip("one GPU on this box (run with gpurun --gpus 2)")
+    cwd, k, frames = scene
+    base = ["-c", "kinect_intrinsic.txt", "--type", "pinhole-depth", "--devices", "2",
+            "-i", "data{}-depth.png", "-s", "0", "-e", "4"]
+    for sub, feat, out in (("max-curve", F_MAX_CURVE, "dev2-mc-{}.png"), ("flexion", F_FLEXION, "dev2-fl-{}.png")):
+        r = run(base + [sub, "-o", out], cwd)
+        assert r.returncode == 0, r.stderr
+        for i in range(5):
+            assert_u16_parity(sub, read(cwd, out.format(i)), oracle.cli_frame(feat, 0, frames[i], k)[2])
