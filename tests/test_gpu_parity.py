@@ -291,3 +291,30 @@ def test_kernel_selection_is_reported(pkg, gpu_ctx, oracle):
     small = np.stack([oracle.synth_depth(0xD2C00002, 0, 322, 203)])
     gpu_ctx.convert(pkg.DC_BEARING, small, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16, want=(True,) * 4)
     assert gpu_ctx.last_kernel.startswith("dc::feature_kernel")
+
+
+@pytest.mark.parametrize("w,h", [(360, 90), (128, 64), (61, 37)])
+def test_equirectangular_float_against_compiled_reference(pkg, gpu_ctx, oracle, w, h):
+    """Row f1 in float: every feature of the equirectangular camera model
+    (camera_models/equirectangular.h:43-181) against the reference's own templates
+    (oracle/_ref). The laser-scan input is a range image already (conversion/util.h:57-67).
+    Non-pinhole angle tables: the table-driven kernels (per-pixel cosines differ between the
+    two anti-diagonal angles of max-curve, depth_to_max_curve.h:136-139)."""
+    from oracle_lib import RefLib, ref_available
+    if not ref_available():
+        pytest.skip("oracle/_ref is not built")
+    ref = RefLib()
+    tmin, tmax = float(np.float32(0.87)), float(np.float32(2.27))
+    gpu_ctx.set_equirectangular(w, h, tmin, tmax)
+    frames = np.stack([oracle.synth_depth(0xD2C00007, f, w, h) for f in range(3)])
+    f32 = gpu_all_features(pkg, gpu_ctx, frames, pkg.DC_IN_U16_RANGE, pkg.DC_OUT_F32)
+    lib = gpu_all_features(pkg, gpu_ctx, frames.astype(np.float32), pkg.DC_IN_F32_RANGE, pkg.DC_OUT_F32)
+    for i in range(3):
+        rng = np.ascontiguousarray(frames[i].astype(np.float32))
+        for f, name in FEATURE_NAMES.items():
+            if name == "range":
+                continue
+            want = np.empty((h, w), np.float32)
+            ref.lib.ref_feature_equi_f32(f, rng.ctypes.data, w, h, tmin, tmax, want.ctypes.data)
+            assert_float_parity(name, f32[name][i], want)
+            assert_float_parity(name, lib[name][i], want)
