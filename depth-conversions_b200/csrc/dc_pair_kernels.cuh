@@ -17,6 +17,9 @@ constexpr int kPairThreads = 128;
 // 65535/pi and folds s * (Q P) into the rounding FFMA2 (16 FFMA2 per row less).
 // Measured no faster (0.5723 vs 0.5704 ms): the scaled coefficients are register
 // operands instead of immediates. Off.
+#ifndef DC_EDGE_RAD_FADD
+#define DC_EDGE_RAD_FADD 1
+#endif
 #ifndef DC_BEARING_FOLD_Q
 #define DC_BEARING_FOLD_Q 0
 #endif
@@ -602,12 +605,24 @@ struct edge {
     f2 d, y;  // sqrt(rad), refined reciprocal of it
     f2 bc;    // X * Y: zero iff either depth is zero
 };
+template <bool RAD_FADD>
 __device__ __forceinline__ edge edge_shared(f2 x, f2 y, f2 xx, f2 yy, float cu) {
     edge     e;
     const f2 sum = add2(xx, yy);
     e.bc         = mul2(x, y);
-    const f2 t   = mul2(e.bc, B(cu));
-    const f2 rad = fma2(B(-2.0f), t, sum);
+    f2 rad;
+    if constexpr (RAD_FADD && DC_EDGE_RAD_FADD) {
+        // 2 RN(bc cu) == RN(bc (2 cu)) exactly: the doubling moves into the scalar
+        // (loop invariant with ONE cosine) and rad = sum - t2 is an FADD2 with two
+        // register operands (2.07 clocks) instead of an FFMA2 with an immediate
+        // multiplicand (3.7 clocks): 0.975 -> 0.968 ms at 4096x2160. With per-pixel
+        // cosines the extra scalar add per edge makes it slower (1.056 -> 1.074 ms).
+        const f2 t2 = mul2(e.bc, B(cu + cu));
+        rad         = sub2(sum, t2);
+    } else {
+        const f2 t = mul2(e.bc, B(cu));
+        rad        = fma2(B(-2.0f), t, sum);
+    }
     f2       seed;
     e.d = sqrt2(rad, seed);
     e.y = rcp_refine2(e.d, seed);
@@ -774,7 +789,7 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
 #pragma unroll
             for (int j = 0; j < 5; ++j) {
                 const float c = cs_(cs.h[j]);
-                const edge  e = edge_shared(mid.r[j], mid.r[j + 1], mid.s[j], mid.s[j + 1], c);
+                const edge  e = edge_shared<!TAB>(mid.r[j], mid.r[j + 1], mid.s[j], mid.s[j + 1], c);
                 if (j >= 1)  // pixel j looks right; angle_formula (:55-82): back + forward
                     m[j - 1] = add2(hb, edge_end(mid.r[j], yc(mid, j + 1, c), e));
                 if (j <= 3)  // pixel j+1 looks left
@@ -790,7 +805,7 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
         for (int i = 0; i < 4; ++i) {
             const int   c  = i + 1;
             const float co = cs_(cs.v[i]);
-            const edge  e  = edge_shared(mid.r[c], dn.r[c], mid.s[c], dn.s[c], co);
+            const edge  e  = edge_shared<!TAB>(mid.r[c], dn.r[c], mid.s[c], dn.s[c], co);
             if constexpr (STORE)
                 take(i, bv[i], edge_end(mid.r[c], yc(dn, c, co), e));
             bv[i] = edge_end(dn.r[c], yc(mid, c, co), e);
@@ -802,7 +817,7 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
 #pragma unroll
             for (int c = 0; c < 5; ++c) {
                 const float co = cs_(cs.d[c]);
-                const edge  e  = edge_shared(mid.r[c], dn.r[c + 1], mid.s[c], dn.s[c + 1], co);
+                const edge  e  = edge_shared<!TAB>(mid.r[c], dn.r[c + 1], mid.s[c], dn.s[c + 1], co);
                 if (c >= 1) {
                     if constexpr (STORE)
                         take(c - 1, bd[c - 1], edge_end(mid.r[c], yc(dn, c + 1, co), e));
@@ -819,7 +834,7 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
 #pragma unroll
         for (int c = 1; c < 6; ++c) {
             if constexpr (!TAB) {
-                const edge e = edge_shared(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], cu);
+                const edge e = edge_shared<!TAB>(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], cu);
                 if constexpr (STORE)
                     if (c <= 4)
                         take(c - 1, ba[c - 1], edge_end(mid.r[c], dn.c[c - 1], e));
@@ -829,12 +844,12 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
                 if constexpr (STORE)
                     if (c <= 4) {
                         const float co = cs.d[c];  // D(u + 1, v + 1), u = u0 + c - 1
-                        const edge  e  = edge_shared(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], co);
+                        const edge  e  = edge_shared<!TAB>(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], co);
                         take(c - 1, ba[c - 1], edge_end(mid.r[c], mul2(dn.r[c - 1], B(co)), e));
                     }
                 if (c >= 2) {
                     const float co = cs.a[c - 2];  // A(u0 + c - 1, v)
-                    const edge  e  = edge_shared(dn.r[c - 1], mid.r[c], dn.s[c - 1], mid.s[c], co);
+                    const edge  e  = edge_shared<!TAB>(dn.r[c - 1], mid.r[c], dn.s[c - 1], mid.s[c], co);
                     ba[c - 2]      = edge_end(dn.r[c - 1], mul2(mid.r[c], B(co)), e);
                 }
             }
