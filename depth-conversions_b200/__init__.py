@@ -31,8 +31,11 @@ EXPORTED_SYMBOLS = [
     "dc_height", "dc_convert_device", "dc_convert_host", "dc_synchronize",
     "dc_host_alloc", "dc_host_free", "dc_synth_depth_device", "dc_kernel_launches", "dc_last_kernel",
     "dc_quantise_host", "dc_set_pinhole_f64", "dc_set_equirectangular_f64",
-    "dc_quantise_host_f64", "dc_median_host", "dc_median_device",
+    "dc_quantise_host_f64", "dc_median_host", "dc_median_device", "dc_f32_fallbacks",
+    "dc_quantise_host_ex",
 ]
+DC_PX_U16, DC_PX_U8, DC_PX_I8, DC_PX_I16 = range(4)
+_PX_DTYPE = {DC_PX_U16: np.uint16, DC_PX_U8: np.uint8, DC_PX_I8: np.int8, DC_PX_I16: np.int16}
 DC_Q_RANGE, DC_Q_BEARING, DC_Q_FLEXION, DC_Q_CURVATURE, DC_Q_MAX_CURVE = range(5)
 
 
@@ -97,6 +100,11 @@ def lib():
         L.dc_kernel_launches.argtypes = [C.c_void_p]
         L.dc_last_kernel.restype = C.c_char_p
         L.dc_last_kernel.argtypes = [C.c_void_p]
+        L.dc_quantise_host_ex.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                          C.c_void_p, C.c_size_t, C.c_void_p,
+                                          C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        L.dc_f32_fallbacks.restype = C.c_uint64
+        L.dc_f32_fallbacks.argtypes = [C.c_void_p]
         _lib = L
     return _lib
 
@@ -169,6 +177,11 @@ class Context:
     def last_kernel(self):
         return self._L.dc_last_kernel(self._h).decode()
 
+    @property
+    def f32_fallbacks(self):
+        """Batches of f32 range input the IEEE kernels had to redo (dc_f32_fallbacks)."""
+        return int(self._L.dc_f32_fallbacks(self._h))
+
     def synchronize(self):
         self._check(self._L.dc_synchronize(self._h))
 
@@ -238,6 +251,26 @@ class Context:
         self._check(self._L.dc_quantise_host(self._h, quant, feature.ctypes.data,
                                              m.ctypes.data if m is not None else None,
                                              feature.size, out.ctypes.data, clamp[0], clamp[1]))
+        return out
+
+    def quantise_ex_raw(self, quant, feature, mask=None, pixel=DC_PX_U16, lo=None, hi=None):
+        """dc_quantise_host_ex: any pixel type; lo / hi None = std::nullopt (curvature:
+        the image's own minimum / maximum). Returns (status, image)."""
+        feature = np.ascontiguousarray(feature)
+        real = DC_OUT_F64 if feature.dtype == np.float64 else DC_OUT_F32
+        feature = feature.astype(np.float64 if real == DC_OUT_F64 else np.float32, copy=False)
+        m = np.ascontiguousarray(mask, feature.dtype) if mask is not None else None
+        out = np.zeros(feature.shape, _PX_DTYPE[pixel])
+        plo = C.byref(C.c_double(lo)) if lo is not None else None
+        phi = C.byref(C.c_double(hi)) if hi is not None else None
+        rc = self._L.dc_quantise_host_ex(self._h, quant, pixel, real, feature.ctypes.data,
+                                         m.ctypes.data if m is not None else None, feature.size,
+                                         out.ctypes.data, plo, phi)
+        return rc, out
+
+    def quantise_ex(self, quant, feature, mask=None, pixel=DC_PX_U16, lo=None, hi=None):
+        rc, out = self.quantise_ex_raw(quant, feature, mask, pixel, lo, hi)
+        self._check(rc)
         return out
 
     def synth_depth_device(self, seed, frame0, n_frames, out_ptr, stream=None):

@@ -1,9 +1,9 @@
 // C ABI of libdepthconv_b200.so: context, per-camera device tables, kernel
 // dispatch and the host-buffer pipeline. See include/depthconv_b200.h.
 #include "../../include/depthconv_b200.h"
-#include "dc_kernels.cuh"
+#include "dc_launch.h"
 #include "dc_median.cuh"
-#include "dc_pair_kernels.cuh"
+#include "dc_misc_kernels.cuh"
 #include "dc_f64.h"
 #include "dc_tables.h"
 
@@ -70,6 +70,13 @@ struct dc_ctx {
     // filtered copy of the input frames (dc_job::median_ksize), one per stream:
     // the chunks of dc_convert_host run concurrently on the slots' streams
     std::map<cudaStream_t, dev_buf> d_median;
+    // f32 range input on the guard-free kernels (dc_kernels.cuh kparams::guard):
+    // a ring of flags, one per launch in flight, and the count of batches the IEEE
+    // kernel had to redo (dc_f32_fallbacks)
+    static constexpr int kGuards = 256;
+    int*                 d_guard     = nullptr;
+    unsigned long long*  d_fallbacks = nullptr;
+    unsigned             next_guard  = 0;
 };
 
 namespace {
@@ -180,6 +187,11 @@ int ensure_tables(dc_ctx* c, unsigned need) {
         if (rc == DC_OK)
             rc = upload(c, c->d_curv[2], c->tabs.d_phi_theta);
     }
+    // The sources are pageable: cudaMemcpy may return once they are staged, before
+    // the DMA has landed, and the kernels run on non-blocking streams that are not
+    // ordered after the legacy stream. Wait for the copies before anything launches.
+    if (rc == DC_OK)
+        DC_CUDA(c, cudaDeviceSynchronize());
     if (rc == DC_OK)
         c->uploaded |= missing;
     return rc;
@@ -270,247 +282,7 @@ int validate_job(dc_ctx* c, const dc_job* j) {
     return DC_OK;
 }
 
-// ---------------------------------------------------------------------------
 bool aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
-
-// Which kernel family the launch helpers below picked (dc_last_kernel: tests and
-// bench.py name the kernel they measured instead of guessing it).
-thread_local const char* g_kernel = "";
-
-// Rows a thread of the frame-pair kernels marches over (tuning knob:
-// DC_ROWS_PER_STRIP in the environment, read once).
-int rows_per_strip() {
-    static const int v = [] {
-        const char* e = std::getenv("DC_ROWS_PER_STRIP");
-        const int   n = e != nullptr ? std::atoi(e) : 0;
-        return n >= 3 ? n : 18;
-    }();
-    return v;
-}
-
-template <int FEAT>
-constexpr bool has_pair_kernel() {
-    return FEAT == dc::FEAT_BEARING || FEAT == dc::FEAT_MAX_CURVE || FEAT == dc::FEAT_CURVATURE;
-}
-
-// The frame-pair row-marching kernels (dc_pair_kernels.cuh): u16 input,
-// width % 4 == 0, aligned frames, per-camera range proof.
-// What is known about a job before the launch (dc_pair.cuh SPEC_*): with all
-// outputs wanted and the camera tables of the feature either all per-pixel
-// arrays or all scalars, the row loop is compiled without pointer tests.
-template <int FEAT, int IN>
-int pair_spec(const dc::kparams& p) {
-    if (IN == dc::IN_U16_DEPTH && p.range_factor.p == nullptr)
-        return dc::pr::SPEC_GENERIC;
-    int tables = 0, scalars = 0;
-    auto see = [&](const dc::tab_ref& t) { (t.p != nullptr ? tables : scalars) += 1; };
-    if (FEAT == dc::FEAT_BEARING || FEAT == dc::FEAT_MAX_CURVE) {
-        for (int d = 0; d < 4; ++d) {
-            if (FEAT == dc::FEAT_BEARING && p.out[d] == nullptr)
-                return dc::pr::SPEC_GENERIC;
-            see(p.cosp[d]);
-        }
-    } else if (FEAT == dc::FEAT_CURVATURE) {
-        if (p.out[0] == nullptr || p.out[1] == nullptr)
-            return dc::pr::SPEC_GENERIC;
-        see(p.d_phi), see(p.d_theta), see(p.d_phi_theta);
-    }
-    return scalars == 0 ? dc::pr::SPEC_TABLES : tables == 0 ? dc::pr::SPEC_UNIFORM : dc::pr::SPEC_GENERIC;
-}
-
-template <int FEAT, int IN, int OUT>
-cudaError_t launch_pair(const dc::kparams& p, int n_frames, cudaStream_t s) {
-    const int       rps    = rows_per_strip();
-    const long long strips = (p.h + rps - 1) / rps;
-    const long long pairs  = (n_frames + 1) / 2;
-    const long long threads = pairs * strips * (p.w / 4);
-    const long long blocks  = (threads + dc::pr::kPairThreads - 1) / dc::pr::kPairThreads;
-    if (blocks > 0x7fffffffLL)
-        return cudaErrorInvalidConfiguration;
-    const dim3   grid{unsigned(blocks)}, block{unsigned(dc::pr::kPairThreads)};
-    static const int forced = [] {
-        const char* e = std::getenv("DC_PAIR_SPEC");  // debugging: 0 forces the generic kernel
-        return e != nullptr ? std::atoi(e) : -1;
-    }();
-    const int spec = forced == 0 ? 0 : pair_spec<FEAT, IN>(p);
-    if constexpr (FEAT == dc::FEAT_MAX_CURVE) {
-        // The kernel that computes every pixel-pair edge once for both of its ends
-        // (dc_pair_kernels.cuh maxcurve_edge_kernel): one scalar for all four
-        // neighbour-angle tables (1080p and larger with Kinect-like intrinsics), or
-        // four per-pixel tables (the anti-diagonal pair is not shared there).
-        static const int edge_rows = [] {
-            const char* e = std::getenv("DC_MCE_ROWS");  // 0 disables the kernel
-            return e != nullptr ? std::atoi(e) : 36;
-        }();
-        auto bits = [](float v) {
-            unsigned u;
-            std::memcpy(&u, &v, sizeof u);
-            return u;
-        };
-        const unsigned c0 = bits(p.cosp[0].value);
-        const bool one_cos = spec == dc::pr::SPEC_UNIFORM && c0 == bits(p.cosp[1].value) &&
-                             c0 == bits(p.cosp[2].value) && c0 == bits(p.cosp[3].value);
-        if (edge_rows >= 3 && (one_cos || spec == dc::pr::SPEC_TABLES)) {
-            const long long estrips  = (p.h + edge_rows - 1) / edge_rows;
-            const long long ethreads = pairs * estrips * (p.w / 4);
-            const long long eblocks  = (ethreads + dc::pr::kPairThreads - 1) / dc::pr::kPairThreads;
-            if (eblocks > 0x7fffffffLL)
-                return cudaErrorInvalidConfiguration;
-            if (one_cos) {
-                dc::pr::maxcurve_edge_kernel<IN, OUT, dc::pr::SPEC_UNIFORM>
-                    <<<unsigned(eblocks), block, dc::pr::mce_smem_bytes<dc::pr::SPEC_UNIFORM>(), s>>>(
-                        p, n_frames, edge_rows);
-                g_kernel = "dc::pr::maxcurve_edge_kernel<SPEC_UNIFORM>";
-            } else {
-                constexpr size_t smem = dc::pr::mce_smem_bytes<dc::pr::SPEC_TABLES>();  // 54 KB
-                // per device, hence not cached in a static (depth2x --devices N runs
-                // one context per GPU in one process); a few microseconds per launch
-                const cudaError_t attr = cudaFuncSetAttribute(
-                    dc::pr::maxcurve_edge_kernel<IN, OUT, dc::pr::SPEC_TABLES>,
-                    cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-                if (attr != cudaSuccess)
-                    return attr;
-                dc::pr::maxcurve_edge_kernel<IN, OUT, dc::pr::SPEC_TABLES>
-                    <<<unsigned(eblocks), block, smem, s>>>(p, n_frames, edge_rows);
-                g_kernel = "dc::pr::maxcurve_edge_kernel<SPEC_TABLES>";
-            }
-            return cudaGetLastError();
-        }
-    }
-    g_kernel = spec == dc::pr::SPEC_TABLES    ? "dc::pr::pair_kernel<SPEC_TABLES>"
-               : spec == dc::pr::SPEC_UNIFORM ? "dc::pr::pair_kernel<SPEC_UNIFORM>"
-                                              : "dc::pr::pair_kernel<SPEC_GENERIC>";
-    switch (spec) {
-    case dc::pr::SPEC_TABLES:
-        dc::pr::pair_kernel<FEAT, IN, OUT, dc::pr::SPEC_TABLES>
-            <<<grid, block, dc::pr::pair_smem_bytes<FEAT, dc::pr::SPEC_TABLES>(), s>>>(p, n_frames, rps);
-        break;
-    case dc::pr::SPEC_UNIFORM:
-        dc::pr::pair_kernel<FEAT, IN, OUT, dc::pr::SPEC_UNIFORM>
-            <<<grid, block, dc::pr::pair_smem_bytes<FEAT, dc::pr::SPEC_UNIFORM>(), s>>>(p, n_frames, rps);
-        break;
-    default:
-        dc::pr::pair_kernel<FEAT, IN, OUT, dc::pr::SPEC_GENERIC>
-            <<<grid, block, dc::pr::pair_smem_bytes<FEAT, dc::pr::SPEC_GENERIC>(), s>>>(p, n_frames, rps);
-    }
-    return cudaGetLastError();
-}
-
-template <int IN, int OUT>
-cudaError_t launch_flexion_pair(const dc::kparams& p, int n_frames, cudaStream_t s) {
-    // a longer march amortises the point window (three rows of camera-frame points
-    // per strip start): 72 rows measured 1.5 % faster than 36 (DC_FLEX_ROWS, read once)
-    static const int flex_rows = [] {
-        const char* e = std::getenv("DC_FLEX_ROWS");
-        const int   n = e != nullptr ? std::atoi(e) : 0;
-        return n >= 3 ? n : 4 * rows_per_strip();
-    }();
-    const int       rps     = flex_rows;
-    const long long strips  = (p.h + rps - 1) / rps;
-    const long long pairs   = (n_frames + 1) / 2;
-    const long long threads = pairs * strips * (p.w / 2);
-    const long long blocks  = (threads + dc::pr::kPairThreads - 1) / dc::pr::kPairThreads;
-    if (blocks > 0x7fffffffLL)
-        return cudaErrorInvalidConfiguration;
-    // per device (one context per GPU in a depth2x --devices N process): not cached
-    const cudaError_t carve = cudaFuncSetAttribute(
-        dc::pr::flexion_pair_kernel<IN, OUT>, cudaFuncAttributePreferredSharedMemoryCarveout,
-        int(cudaSharedmemCarveoutMaxShared));
-    if (carve != cudaSuccess)
-        return carve;
-    const size_t smem = size_t(3) * dc::pr::kFlexSlots * dc::pr::kPairThreads * sizeof(uint4);
-    g_kernel = "dc::pr::flexion_pair_kernel";
-    dc::pr::flexion_pair_kernel<IN, OUT>
-        <<<unsigned(blocks), dc::pr::kPairThreads, smem, s>>>(p, n_frames, rps);
-    return cudaGetLastError();
-}
-
-// DC_RANGE / DC_SCALE with u16 input: the streaming kernel (8 pixels per thread,
-// frames walked inside the thread). Needs frames that are multiples of 8 pixels
-// and 16-byte aligned buffers.
-template <int FEAT, int IN, int OUT>
-cudaError_t launch_stream(const dc::kparams& p, int n_frames, cudaStream_t s) {
-    const int groups = int(p.frame_px / 8);
-    const int bx     = (groups + 255) / 256;
-    // about 8 resident blocks per SM; at least 4 frames per thread when possible
-    int by = std::max(1, std::min((148 * 8 + bx - 1) / bx, (n_frames + 3) / 4));
-    by     = std::min(by, 65535);
-    g_kernel = "dc::pr::stream_kernel";
-    dc::pr::stream_kernel<FEAT, IN, OUT><<<dim3(bx, by, 1), 256, 0, s>>>(p, n_frames, groups);
-    return cudaGetLastError();
-}
-
-template <int FEAT, int IN, int OUT>
-cudaError_t launch_px(const dc::kparams& p, int n_frames, cudaStream_t s, bool vec4, bool fast) {
-    if constexpr (IN != dc::IN_F32_RANGE && (FEAT == dc::FEAT_RANGE || FEAT == dc::FEAT_SCALE)) {
-        bool ok = vec4 && (p.frame_px % 8) == 0 && aligned(p.in, 16) && aligned(p.out[0], 16);
-        if (ok)
-            return launch_stream<FEAT, IN, OUT>(p, n_frames, s);
-    }
-    if constexpr (IN != dc::IN_F32_RANGE && has_pair_kernel<FEAT>()) {
-        if (vec4 && fast)
-            return launch_pair<FEAT, IN, OUT>(p, n_frames, s);
-    }
-    if constexpr (IN != dc::IN_F32_RANGE && FEAT == dc::FEAT_FLEXION) {
-        if (vec4 && fast)
-            return launch_flexion_pair<IN, OUT>(p, n_frames, s);
-    }
-    g_kernel = vec4 && fast ? "dc::feature_kernel<4, fast>" : vec4 ? "dc::feature_kernel<4>" : "dc::feature_kernel<1>";
-    const int px = vec4 ? 4 : 1;
-    const int qw = (p.w + px - 1) / px;
-    // pick the block shape that wastes the fewest threads
-    static const int shapes[4][2] = {{32, 8}, {16, 16}, {64, 4}, {8, 32}};
-    int       best = 0;
-    long long best_cost = -1;
-    for (int i = 0; i < 4; ++i) {
-        const long long gx = (qw + shapes[i][0] - 1) / shapes[i][0];
-        const long long gy = (p.h + shapes[i][1] - 1) / shapes[i][1];
-        const long long cost = gx * gy;
-        if (best_cost < 0 || cost < best_cost) {
-            best_cost = cost;
-            best      = i;
-        }
-    }
-    const dim3 block(shapes[best][0], shapes[best][1], 1);
-    const unsigned gx = (qw + block.x - 1) / block.x, gy = (p.h + block.y - 1) / block.y;
-    const size_t   in_b = IN == dc::IN_F32_RANGE ? 4 : 2, out_b = OUT == dc::OUT_F32 ? 4 : 2;
-    for (int f0 = 0; f0 < n_frames; f0 += 65535) {
-        const int   nf = std::min(65535, n_frames - f0);
-        dc::kparams q  = p;
-        q.in           = static_cast<const char*>(p.in) + size_t(f0) * p.frame_px * in_b;
-        for (int k = 0; k < 4; ++k)
-            if (p.out[k] != nullptr)
-                q.out[k] = static_cast<char*>(p.out[k]) + size_t(f0) * p.frame_px * out_b;
-        const dim3 grid(gx, gy, unsigned(nf));
-        if (vec4 && fast)
-            dc::feature_kernel<FEAT, IN, OUT, 4, true><<<grid, block, 0, s>>>(q);
-        else if (vec4)
-            dc::feature_kernel<FEAT, IN, OUT, 4, false><<<grid, block, 0, s>>>(q);
-        else
-            dc::feature_kernel<FEAT, IN, OUT, 1, false><<<grid, block, 0, s>>>(q);
-        const cudaError_t e = cudaGetLastError();
-        if (e != cudaSuccess)
-            return e;
-    }
-    return cudaSuccess;
-}
-
-template <int FEAT, int IN>
-cudaError_t launch_out(const dc::kparams& p, int out_kind, int n, cudaStream_t s, bool v4,
-                       bool fast) {
-    return out_kind == DC_OUT_F32 ? launch_px<FEAT, IN, dc::OUT_F32>(p, n, s, v4, fast)
-                                  : launch_px<FEAT, IN, dc::OUT_U16>(p, n, s, v4, fast);
-}
-template <int FEAT>
-cudaError_t launch_in(const dc::kparams& p, int in_kind, int out_kind, int n, cudaStream_t s,
-                      bool v4, bool fast) {
-    switch (in_kind) {
-    case DC_IN_U16_DEPTH: return launch_out<FEAT, dc::IN_U16_DEPTH>(p, out_kind, n, s, v4, fast);
-    case DC_IN_U16_RANGE: return launch_out<FEAT, dc::IN_U16_RANGE>(p, out_kind, n, s, v4, fast);
-    default: return launch_out<FEAT, dc::IN_F32_RANGE>(p, out_kind, n, s, v4, false);
-    }
-}
-
 
 // Enqueue the fused kernel(s) for `job` (device pointers) on stream `s`.
 int launch_job(dc_ctx* c, const dc_job* j, cudaStream_t s) {
@@ -593,31 +365,47 @@ int launch_job(dc_ctx* c, const dc_job* j, cudaStream_t s) {
     p.s_scale         = float(j->scale);
     p.s_offset        = float(j->offset);
 
-    // vector path: rows and frames must keep 8-byte (u16) / 16-byte (f32) alignment
-    bool v4 = (w % 4) == 0;
-    v4      = v4 && aligned(j->in, in_kind == DC_IN_F32_RANGE ? 16 : 8);
+    // vector paths: rows and frames must keep 8-byte (u16) / 16-byte (f32) alignment
+    // for a width that is a multiple of four, half of that for any other even width
+    const size_t in_al  = in_kind == DC_IN_F32_RANGE ? 16 : 8;
+    const size_t out_al = j->out_kind == DC_OUT_F32 ? 16 : 8;
+    dc::launch_info li{};
+    li.vec4 = (w % 4) == 0 && aligned(j->in, in_al);
+    li.even = (w % 2) == 0 && aligned(j->in, in_al / 2);
     for (int k = 0; k < 4; ++k)
-        if (j->out[k] != nullptr)
-            v4 = v4 && aligned(j->out[k], j->out_kind == DC_OUT_F32 ? 16 : 8);
-
+        if (j->out[k] != nullptr) {
+            li.vec4 = li.vec4 && aligned(j->out[k], out_al);
+            li.even = li.even && aligned(j->out[k], out_al / 2);
+        }
     // guard-free exact arithmetic needs the per-camera range proof (dc_tables)
-    const bool fast = c->tabs.fast_ok;
-    cudaError_t e = cudaSuccess;
+    li.fast = c->tabs.fast_ok;
+    if (in_kind == DC_IN_F32_RANGE) {
+        if (c->d_guard == nullptr) {
+            DC_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->d_guard), dc_ctx::kGuards * sizeof(int)));
+            DC_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->d_fallbacks), sizeof(unsigned long long)));
+            DC_CUDA(c, cudaMemset(c->d_fallbacks, 0, sizeof(unsigned long long)));
+            DC_CUDA(c, cudaDeviceSynchronize());
+        }
+        p.guard     = c->d_guard + (c->next_guard++ % dc_ctx::kGuards);
+        p.fallbacks = c->d_fallbacks;
+    }
+    const int   ik = in_kind == DC_IN_U16_DEPTH ? dc::IN_U16_DEPTH
+                     : in_kind == DC_IN_U16_RANGE ? dc::IN_U16_RANGE : dc::IN_F32_RANGE;
+    const int   ok = j->out_kind == DC_OUT_F32 ? dc::OUT_F32 : dc::OUT_U16;
+    cudaError_t e  = cudaSuccess;
     switch (j->feature) {
-    case DC_RANGE: e = launch_in<dc::FEAT_RANGE>(p, in_kind, j->out_kind, j->n_frames, s, v4, fast); break;
-    case DC_BEARING: e = launch_in<dc::FEAT_BEARING>(p, in_kind, j->out_kind, j->n_frames, s, v4, fast); break;
-    case DC_FLEXION: e = launch_in<dc::FEAT_FLEXION>(p, in_kind, j->out_kind, j->n_frames, s, v4, fast); break;
-    case DC_CURVATURE: e = launch_in<dc::FEAT_CURVATURE>(p, in_kind, j->out_kind, j->n_frames, s, v4, fast); break;
-    case DC_MAX_CURVE: e = launch_in<dc::FEAT_MAX_CURVE>(p, in_kind, j->out_kind, j->n_frames, s, v4, fast); break;
-    case DC_SCALE:
-        e = launch_px<dc::FEAT_SCALE, dc::IN_U16_RANGE, dc::OUT_U16>(p, j->n_frames, s, v4, false);
-        break;
+    case DC_RANGE: e = dc::launch_range(p, ik, ok, j->n_frames, s, li); break;
+    case DC_BEARING: e = dc::launch_bearing(p, ik, ok, j->n_frames, s, li); break;
+    case DC_FLEXION: e = dc::launch_flexion(p, ik, ok, j->n_frames, s, li); break;
+    case DC_CURVATURE: e = dc::launch_curvature(p, ik, ok, j->n_frames, s, li); break;
+    case DC_MAX_CURVE: e = dc::launch_max_curve(p, ik, ok, j->n_frames, s, li); break;
+    case DC_SCALE: e = dc::launch_scale(p, j->n_frames, s, li); break;
     default: return fail(c, DC_ERR_INVALID, "unknown feature");
     }
     if (e != cudaSuccess)
         return cuda_fail(c, e, "kernel launch");
-    c->launches += uint64_t((j->n_frames + 65534) / 65535);
-    c->last_kernel = g_kernel;
+    c->launches += uint64_t(li.launches);
+    c->last_kernel = li.kernel;
     return DC_OK;
 }
 
@@ -643,6 +431,45 @@ int finish_slot(dc_ctx* c, slot& s) {
     return DC_OK;
 }
 
+}  // namespace
+
+namespace {
+template <typename Real, typename Px>
+cudaError_t run_quantise(int quant, const void* in, const void* mask, size_t n, void* out,
+                         double max_value, double lo, double hi, cudaStream_t s) {
+    // conversion/util.h:71-79 scaling_factor<Real, PixelType>(max): both factors
+    // computed in Real, as the reference does
+    const Real pmin = Real(dc::px_limits<Px>::lo), pmax = Real(dc::px_limits<Px>::hi);
+    const Real alpha = (pmax - pmin) / Real(max_value), offset = pmin;
+    const unsigned blocks = unsigned(std::min<size_t>((n + 255) / 256, 148 * 16));
+    dc::quantise_kernel<Real, Px><<<blocks, 256, 0, s>>>(
+        quant, static_cast<const Real*>(in), static_cast<const Real*>(mask), n,
+        static_cast<Px*>(out), alpha, offset, Real(lo), Real(hi));
+    return cudaGetLastError();
+}
+template <typename Real>
+cudaError_t run_quantise_px(int quant, int pixel, const void* in, const void* mask, size_t n,
+                            void* out, double max_value, double lo, double hi, cudaStream_t s) {
+    switch (pixel) {
+    case DC_PX_U8: return run_quantise<Real, unsigned char>(quant, in, mask, n, out, max_value, lo, hi, s);
+    case DC_PX_I8: return run_quantise<Real, signed char>(quant, in, mask, n, out, max_value, lo, hi, s);
+    case DC_PX_I16: return run_quantise<Real, short>(quant, in, mask, n, out, max_value, lo, hi, s);
+    default: return run_quantise<Real, unsigned short>(quant, in, mask, n, out, max_value, lo, hi, s);
+    }
+}
+// decode of dc::ordered<Real>::enc
+float dec_ordered(unsigned e) {
+    const unsigned u = (e & 0x80000000u) ? (e & 0x7fffffffu) : ~e;
+    float f;
+    std::memcpy(&f, &u, sizeof f);
+    return f;
+}
+double dec_ordered(unsigned long long e) {
+    const unsigned long long u = (e >> 63) ? (e & 0x7fffffffffffffffull) : ~e;
+    double f;
+    std::memcpy(&f, &u, sizeof f);
+    return f;
+}
 }  // namespace
 
 // ===========================================================================
@@ -711,6 +538,10 @@ void dc_destroy(dc_ctx* c) {
     dc64::destroy(c->f64);
     for (auto& kv : c->d_median)
         free_dev(kv.second);
+    if (c->d_guard != nullptr)
+        cudaFree(c->d_guard);
+    if (c->d_fallbacks != nullptr)
+        cudaFree(c->d_fallbacks);
     for (auto& s : c->slots) {
         free_dev(s.d_in);
         free_pinned(s.h_in);
@@ -927,91 +758,106 @@ int dc_convert_host(dc_ctx* c, const dc_job* j) {
     return DC_OK;
 }
 
-int dc_quantise_host(dc_ctx* c, int quant, const float* feature, const float* mask, size_t n_px,
-                     uint16_t* out, float clamp_lo, float clamp_hi) {
+int dc_quantise_host_ex(dc_ctx* c, int quant, int pixel, int real_kind, const void* feature,
+                        const void* mask, size_t n_px, void* out, const double* clamp_lo,
+                        const double* clamp_hi) {
     if (c == nullptr)
         return DC_ERR_INVALID;
     if (c->sticky)
         return DC_ERR_CUDA;
     if (quant < DC_Q_RANGE || quant > DC_Q_MAX_CURVE)
         return fail(c, DC_ERR_INVALID, "unknown quantiser");
+    if (pixel < DC_PX_U16 || pixel > DC_PX_I16)
+        return fail(c, DC_ERR_INVALID, "unknown pixel type");
+    if (real_kind != DC_OUT_F32 && real_kind != DC_OUT_F64)
+        return fail(c, DC_ERR_INVALID, "real_kind is DC_OUT_F32 or DC_OUT_F64");
     if (n_px == 0)
         return DC_OK;
     if (feature == nullptr || out == nullptr)
         return fail(c, DC_ERR_INVALID, "quantiser buffers are NULL");
-    if (quant == DC_Q_CURVATURE && (mask == nullptr || !(clamp_lo < clamp_hi)))
-        return fail(c, DC_ERR_INVALID,
-                    "curvature quantiser needs the range image as mask and lower < upper bound");
+    if (quant == DC_Q_CURVATURE && mask == nullptr)
+        return fail(c, DC_ERR_INVALID, "curvature quantiser needs the range image as mask");
+    if (quant == DC_Q_CURVATURE && pixel != DC_PX_U16)
+        return fail(c, DC_ERR_UNSUPPORTED,
+                    "curvature_to_image yields 16 bit images only (depth_to_curvature.h:263-275: "
+                    "the ushort intermediate re-types the result)");
+    if (quant == DC_Q_RANGE && pixel != DC_PX_U16)
+        return fail(c, DC_ERR_UNSUPPORTED, "the range image is written as 16 bit (converter_laserscan.h.inl:9-10)");
     DC_CUDA(c, cudaSetDevice(c->device));
-    slot& s = c->slots[0];
-    int   rc = finish_slot(c, s);
+    const bool   f64 = real_kind == DC_OUT_F64;
+    const size_t rb = f64 ? 8 : 4, pb = (pixel == DC_PX_U8 || pixel == DC_PX_I8) ? 1 : 2;
+    slot&        s  = c->slots[0];
+    int          rc = finish_slot(c, s);
     if (rc != DC_OK)
         return rc;
-    DC_CUDA(c, reserve_dev(s.d_in, n_px * sizeof(float)));
-    DC_CUDA(c, reserve_dev(s.d_out[0], n_px * sizeof(float)));
-    DC_CUDA(c, reserve_dev(s.d_out[1], n_px * sizeof(uint16_t)));
-    DC_CUDA(c, cudaMemcpyAsync(s.d_in.p, feature, n_px * sizeof(float), cudaMemcpyHostToDevice,
-                               s.stream));
-    if (quant == DC_Q_CURVATURE)
-        DC_CUDA(c, cudaMemcpyAsync(s.d_out[0].p, mask, n_px * sizeof(float),
-                                   cudaMemcpyHostToDevice, s.stream));
-    // conversion/util.h:71-79 scaling_factor<float, ushort>(max_angle)
-    const float pi_f  = float(3.141592653589793238462);
-    const float alpha = quant == DC_Q_BEARING     ? 65535.0f / pi_f
-                        : quant == DC_Q_MAX_CURVE ? 65535.0f / float(2. * double(pi_f))
-                                                  : 65535.0f;
-    const unsigned blocks = unsigned(std::min<size_t>((n_px + 255) / 256, 148 * 16));
-    dc::quantise_kernel<<<blocks, 256, 0, s.stream>>>(
-        quant, static_cast<const float*>(s.d_in.p), static_cast<const float*>(s.d_out[0].p), n_px,
-        static_cast<unsigned short*>(s.d_out[1].p), alpha, clamp_lo, clamp_hi);
-    const cudaError_t e = cudaGetLastError();
+    DC_CUDA(c, reserve_dev(s.d_in, n_px * rb));
+    DC_CUDA(c, reserve_dev(s.d_out[0], n_px * rb));
+    DC_CUDA(c, reserve_dev(s.d_out[1], n_px * pb));
+    DC_CUDA(c, cudaMemcpyAsync(s.d_in.p, feature, n_px * rb, cudaMemcpyHostToDevice, s.stream));
+    double lo = clamp_lo != nullptr ? *clamp_lo : 0., hi = clamp_hi != nullptr ? *clamp_hi : 0.;
+    if (quant == DC_Q_CURVATURE) {
+        DC_CUDA(c, cudaMemcpyAsync(s.d_out[0].p, mask, n_px * rb, cudaMemcpyHostToDevice, s.stream));
+        if (clamp_lo == nullptr || clamp_hi == nullptr) {
+            // depth_to_curvature.h:218-228: a missing clamp is the image's own
+            // minimum / maximum (std::minmax_element over every pixel)
+            DC_CUDA(c, reserve_dev(s.d_out[2], 16));
+            const unsigned long long init64[2] = {~0ull, 0ull};
+            const unsigned           init32[2] = {~0u, 0u};
+            DC_CUDA(c, cudaMemcpyAsync(s.d_out[2].p, f64 ? static_cast<const void*>(init64) : init32,
+                                       f64 ? 16 : 8, cudaMemcpyHostToDevice, s.stream));
+            const unsigned blocks = unsigned(std::min<size_t>((n_px + 255) / 256, 148 * 8));
+            if (f64)
+                dc::minmax_kernel<double><<<blocks, 256, 0, s.stream>>>(
+                    static_cast<const double*>(s.d_in.p), n_px, static_cast<unsigned long long*>(s.d_out[2].p));
+            else
+                dc::minmax_kernel<float><<<blocks, 256, 0, s.stream>>>(
+                    static_cast<const float*>(s.d_in.p), n_px, static_cast<unsigned*>(s.d_out[2].p));
+            const cudaError_t e = cudaGetLastError();
+            if (e != cudaSuccess)
+                return cuda_fail(c, e, "min/max kernel launch");
+            c->launches += 1;
+            unsigned long long r64[2];
+            unsigned           r32[2];
+            DC_CUDA(c, cudaMemcpyAsync(f64 ? static_cast<void*>(r64) : r32, s.d_out[2].p, f64 ? 16 : 8,
+                                       cudaMemcpyDeviceToHost, s.stream));
+            DC_CUDA(c, cudaStreamSynchronize(s.stream));
+            const double mn = f64 ? dec_ordered(r64[0]) : double(dec_ordered(r32[0]));
+            const double mx = f64 ? dec_ordered(r64[1]) : double(dec_ordered(r32[1]));
+            if (clamp_lo == nullptr)
+                lo = mn;
+            if (clamp_hi == nullptr)
+                hi = mx;
+        }
+        if (!(lo < hi))  // Expects(source_range.min < source_range.max), math/scaling.h:36
+            return fail(c, DC_ERR_INVALID, "curvature quantiser needs lower bound < upper bound");
+    }
+    const double pi_f = double(float(3.141592653589793238462));
+    // pi<Real> (math/constants.h:8-10); max-curve: Real(2. * pi<Real>) (depth_to_max_curve.h:166)
+    const double pi_r = f64 ? 3.141592653589793238462 : pi_f;
+    const double max_value = quant == DC_Q_BEARING     ? pi_r
+                             : quant == DC_Q_MAX_CURVE ? (f64 ? 2. * pi_r : double(float(2. * pi_r)))
+                                                       : 1.0;
+    const cudaError_t e =
+        f64 ? run_quantise_px<double>(quant, pixel, s.d_in.p, s.d_out[0].p, n_px, s.d_out[1].p, max_value, lo, hi, s.stream)
+            : run_quantise_px<float>(quant, pixel, s.d_in.p, s.d_out[0].p, n_px, s.d_out[1].p, max_value, lo, hi, s.stream);
     if (e != cudaSuccess)
         return cuda_fail(c, e, "quantise kernel launch");
     c->launches += 1;
-    DC_CUDA(c, cudaMemcpyAsync(out, s.d_out[1].p, n_px * sizeof(uint16_t), cudaMemcpyDeviceToHost,
-                               s.stream));
+    DC_CUDA(c, cudaMemcpyAsync(out, s.d_out[1].p, n_px * pb, cudaMemcpyDeviceToHost, s.stream));
     DC_CUDA(c, cudaStreamSynchronize(s.stream));
     return DC_OK;
 }
 
+int dc_quantise_host(dc_ctx* c, int quant, const float* feature, const float* mask, size_t n_px,
+                     uint16_t* out, float clamp_lo, float clamp_hi) {
+    const double lo = clamp_lo, hi = clamp_hi;
+    return dc_quantise_host_ex(c, quant, DC_PX_U16, DC_OUT_F32, feature, mask, n_px, out, &lo, &hi);
+}
+
 int dc_quantise_host_f64(dc_ctx* c, int quant, const double* feature, const double* mask,
                          size_t n_px, uint16_t* out, double clamp_lo, double clamp_hi) {
-    if (c == nullptr)
-        return DC_ERR_INVALID;
-    if (c->sticky)
-        return DC_ERR_CUDA;
-    if (quant < DC_Q_RANGE || quant > DC_Q_MAX_CURVE)
-        return fail(c, DC_ERR_INVALID, "unknown quantiser");
-    if (n_px == 0)
-        return DC_OK;
-    if (feature == nullptr || out == nullptr)
-        return fail(c, DC_ERR_INVALID, "quantiser buffers are NULL");
-    if (quant == DC_Q_CURVATURE && (mask == nullptr || !(clamp_lo < clamp_hi)))
-        return fail(c, DC_ERR_INVALID,
-                    "curvature quantiser needs the range image as mask and lower < upper bound");
-    DC_CUDA(c, cudaSetDevice(c->device));
-    slot& s  = c->slots[0];
-    int   rc = finish_slot(c, s);
-    if (rc != DC_OK)
-        return rc;
-    DC_CUDA(c, reserve_dev(s.d_in, n_px * sizeof(double)));
-    DC_CUDA(c, reserve_dev(s.d_out[0], n_px * sizeof(double)));
-    DC_CUDA(c, reserve_dev(s.d_out[1], n_px * sizeof(uint16_t)));
-    DC_CUDA(c, cudaMemcpyAsync(s.d_in.p, feature, n_px * sizeof(double), cudaMemcpyHostToDevice,
-                               s.stream));
-    if (quant == DC_Q_CURVATURE)
-        DC_CUDA(c, cudaMemcpyAsync(s.d_out[0].p, mask, n_px * sizeof(double),
-                                   cudaMemcpyHostToDevice, s.stream));
-    const cudaError_t e = dc64::quantise(
-        quant, static_cast<const double*>(s.d_in.p), static_cast<const double*>(s.d_out[0].p), n_px,
-        static_cast<uint16_t*>(s.d_out[1].p), clamp_lo, clamp_hi, s.stream);
-    if (e != cudaSuccess)
-        return cuda_fail(c, e, "quantise kernel launch");
-    c->launches += 1;
-    DC_CUDA(c, cudaMemcpyAsync(out, s.d_out[1].p, n_px * sizeof(uint16_t), cudaMemcpyDeviceToHost,
-                               s.stream));
-    DC_CUDA(c, cudaStreamSynchronize(s.stream));
-    return DC_OK;
+    return dc_quantise_host_ex(c, quant, DC_PX_U16, DC_OUT_F64, feature, mask, n_px, out, &clamp_lo,
+                               &clamp_hi);
 }
 
 static int median_check(dc_ctx* c, int elem_kind, const void* in, int n_frames, int ksize,
@@ -1131,5 +977,17 @@ int dc_synth_depth_device(dc_ctx* c, uint64_t seed, int frame0, int n_frames,
 uint64_t dc_kernel_launches(const dc_ctx* c) { return c != nullptr ? c->launches : 0; }
 
 const char* dc_last_kernel(const dc_ctx* c) { return c != nullptr ? c->last_kernel : ""; }
+
+uint64_t dc_f32_fallbacks(dc_ctx* c) {
+    if (c == nullptr || c->d_fallbacks == nullptr)
+        return 0;
+    unsigned long long n = 0;
+    if (cudaSetDevice(c->device) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess ||
+        cudaMemcpy(&n, c->d_fallbacks, sizeof n, cudaMemcpyDeviceToHost) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
 
 }  // extern "C"

@@ -160,6 +160,12 @@ static cudaError_t ensure(state* s) {
         if (e != cudaSuccess)
             return e;
     }
+    // pageable sources: the copies may still be in flight when cudaMemcpy returns,
+    // and the kernels run on streams that do not wait for the legacy stream
+    // (and the host tables are freed below)
+    const cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess)
+        return e;
     s->host  = host_tables{};  // the device copies are what is used from here on
     s->built = true;
     return cudaSuccess;
@@ -315,30 +321,6 @@ __global__ void __launch_bounds__(256) feature64_kernel(const kparams64 p) {
     }
 }
 
-// Quantisers on double images: cv::Mat::convertTo(CV_16U, alpha) on a 64F source
-// is saturate_cast<ushort>(src * alpha) = cvRound (half to even) + clamp;
-// curvature: math/scaling.h:29-55 in double, truncation, depth mask.
-__global__ void __launch_bounds__(256)
-    quantise64_kernel(int quant, const double* __restrict__ in, const double* __restrict__ mask,
-                      size_t n, unsigned short* __restrict__ out, double alpha, double lo, double hi) {
-    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
-         i += size_t(gridDim.x) * blockDim.x) {
-        const double v = in[i];
-        if (quant == 3) {  // DC_Q_CURVATURE
-            const double scaled = (65535. * (v - lo)) / (hi - lo) + 0.;
-            const double tc     = fmin(fmax(scaled, 0.), 65535.);
-            // mask: saturate_cast<uchar>(range) != 0
-            const double r  = rint(mask[i]);
-            const bool   on = fmin(fmax(r, 0.), 255.) != 0.;
-            out[i] = on ? (unsigned short)(int)tc : (unsigned short)0;
-        } else {
-            const double s = quant == 0 ? v : v * alpha;
-            const double r = rint(s);  // NaN -> 0 below, like cvRound's INT_MIN
-            out[i] = (unsigned short)(r >= 65535. ? 65535 : (r > 0. ? int(r) : 0));
-        }
-    }
-}
-
 template <int FEAT>
 cudaError_t launch(const kparams64& p, int n_frames, cudaStream_t s) {
     const dim3 block(32, 8, 1);
@@ -399,15 +381,6 @@ cudaError_t convert(state* s, int feature, int in_kind, const void* d_in, int n_
     else
         launches += std::uint64_t((n_frames + 65534) / 65535);
     return e;
-}
-
-cudaError_t quantise(int quant, const double* d_feature, const double* d_mask, std::size_t n,
-                     std::uint16_t* d_out, double lo, double hi, cudaStream_t stream) {
-    // conversion/util.h:71-79 scaling_factor<double, ushort>(max_angle)
-    const double alpha = quant == 1 ? 65535. / kPi : quant == 4 ? 65535. / (2. * kPi) : 65535.;
-    const unsigned blocks = unsigned(std::min<std::size_t>((n + 255) / 256, 148 * 16));
-    quantise64_kernel<<<blocks, 256, 0, stream>>>(quant, d_feature, d_mask, n, d_out, alpha, lo, hi);
-    return cudaGetLastError();
 }
 
 }  // namespace dc64

@@ -33,9 +33,5 @@ cudaError_t convert(state* s, int feature, int in_kind, const void* d_in, int n_
                     double* const d_out[4], cudaStream_t stream, std::string& err,
                     std::uint64_t& launches);
 
-// quant: dc_quant. feature / mask / out are device pointers.
-cudaError_t quantise(int quant, const double* d_feature, const double* d_mask, std::size_t n,
-                     std::uint16_t* d_out, double lo, double hi, cudaStream_t stream);
-
 }  // namespace dc64
 #endif

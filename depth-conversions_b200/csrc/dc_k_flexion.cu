@@ -1,0 +1,8 @@
+// Kernel instantiations of one feature (dc_launch.h): flexion.
+#include "dc_launch.cuh"
+
+namespace dc {
+cudaError_t launch_flexion(const kparams& p, int in_kind, int out_kind, int n, cudaStream_t s, launch_info& li) {
+    return ln::launch_feature<FEAT_FLEXION>(p, in_kind, out_kind, n, s, li);
+}
+}  // namespace dc

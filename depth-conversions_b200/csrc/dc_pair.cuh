@@ -39,7 +39,7 @@ __device__ __forceinline__ f2 neg2(f2 a) { return make_float2(-a.x, -a.y); }
 // fma(a, b, -0.0) with the -0.0 read from constant memory (opaque to ptxas):
 // RN(a*b + -0) == RN(a*b) for every a, b including signed zeros, the cost is
 // the same FMA-pipe slot, and an FFMA2 result cannot be fused into an add.
-__constant__ float k_neg_zero = -0.0f;
+static __constant__ float k_neg_zero = -0.0f;  // (one copy per translation unit)
 __device__ __forceinline__ f2 mul2(f2 a, f2 b) { return __ffma2_rn(a, b, make_float2(k_neg_zero, k_neg_zero)); }
 __device__ __forceinline__ f2 add2(f2 a, f2 b) { return __fadd2_rn(a, b); }
 __device__ __forceinline__ f2 sub2(f2 a, f2 b) { return __fadd2_rn(a, neg2(b)); }
@@ -74,9 +74,13 @@ __device__ __forceinline__ f2 halve2(f2 x) {
 #define DC_APPROX_RATIO 0
 #endif
 __device__ __forceinline__ float mufu_sqrt(float x) {
+#if DC_ABL & 1
+    return x;
+#else
     float y;
     asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
+#endif
 }
 // RN(sqrt(x)) per half (dc_fastmath.cuh sqrt_rn_fast), y = the rsqrt seed.
 __device__ __forceinline__ f2 sqrt2(f2 x, f2& y) {
@@ -111,6 +115,9 @@ __device__ __forceinline__ f2 div2_fast(f2 a, f2 b) { return div2(a, b, rcp_refi
 __device__ __forceinline__ f2 acos_abs2(f2 q) {
     const f2 a = make_float2(fminf(fabsf(q.x), DC_ONE_MINUS_DELTA),
                              fminf(fabsf(q.y), DC_ONE_MINUS_DELTA));
+#if DC_ABL & 4
+    return a;
+#endif
     const f2 t = sub2(B(1.0f), a);
 #if DC_ACOS_MUFU_SQRT
     // MUFU.SQRT (max. relative error 2^-23) instead of t * MUFU.RSQ(t): one
@@ -275,7 +282,10 @@ __device__ __forceinline__ void cp_async_wait_but_one() { asm volatile("cp.async
 //   SPEC_UNIFORM  every output is wanted, every angle table is one scalar (the
 //                 clamp of camera_models/utility.h:39-45, 1080p and larger);
 //                 the range factor of depth input is still an array
-enum { SPEC_GENERIC = 0, SPEC_TABLES = 1, SPEC_UNIFORM = 2 };
+//   SPEC_HALF     SPEC_GENERIC for widths with w % 4 == 2 (rows are only 4-byte
+//                 (u16) / 8-byte (f32) aligned): every 4-pixel access is made as
+//                 two halves, the second one masked in the last column group
+enum { SPEC_GENERIC = 0, SPEC_TABLES = 1, SPEC_UNIFORM = 2, SPEC_HALF = 3 };
 template <int SPEC>
 __device__ __forceinline__ bool is_table(const tab_ref& t) {
     if constexpr (SPEC == SPEC_TABLES)
@@ -287,7 +297,7 @@ __device__ __forceinline__ bool is_table(const tab_ref& t) {
 }
 template <int SPEC>
 __device__ __forceinline__ bool wanted(const void* out) {
-    if constexpr (SPEC != SPEC_GENERIC)
+    if constexpr (SPEC == SPEC_TABLES || SPEC == SPEC_UNIFORM)
         return true;
     else
         return out != nullptr;
@@ -305,78 +315,148 @@ __device__ __forceinline__ bool has_fac(const float* fac) {
 }
 
 constexpr int kRawSlots = 4;
+// u16 input:
 // slot 0: 4 px of frame A | 4 px of frame B        (u16 x 8)
 // slot 1: the u16 pairs holding column u0-1 of A, of B, column u0+4 of A, of B
 // slot 2: range factor of the 4 columns            (f32 x 4)
 // slot 3: range factor of columns u0-1, u0+4       (f32 x 2)
+// f32 range input (no factor):
+// slot 0: 4 px of frame A   slot 1: 4 px of frame B
+// slot 2: [A(u0-1) | B(u0-1) | A(u0+4) | B(u0+4)]
 
 // one input row of the two frames: columns u0-1 .. u0+4
 struct rawrow {
-    uint2    a, b;            // 4 u16 of frame A / B
-    unsigned la, lb, ra, rb;  // words holding the halo pixels (0 outside the image):
+    uint2    a, b;            // u16: 4 pixels of frame A / B
+    unsigned la, lb, ra, rb;  // u16: words holding the halo pixels (0 outside the image):
                               // left pixel in the HIGH half, right pixel in the LOW half
     float4   f;               // range factor of the 4 columns
     float    fl, fr;          // and of the halo columns
+    float4   fa, fb;          // f32: 4 pixels of frame A / B
+    float    hla, hlb, hra, hrb;  // f32: halo pixels
 };
 
 // Per-thread constants of the marching loop: every stream as a pointer to the
 // thread's first column, so that a row is reached by adding one 32-bit row
 // offset; the halo predicates / offsets do not change from row to row.
 struct lane {
-    const unsigned short *A, *Bf;  // frames A and B at column u0
+    const unsigned short *A, *Bf;  // frames A and B at column u0 (u16 input)
+    const float *         Af, *Bff;  // the same for f32 input
     const float*          fac;     // range factor table at column u0 (or nullptr)
     int                   offl, offr;  // element offset of the word holding u0-1 / u0+4
     bool                  hl, hr;      // halo column inside the image
+    bool                  full;        // SPEC_HALF: columns u0+2, u0+3 exist
 };
 
 // Starts the copies of input row `roff / w` (roff = row * w, row clamped into
 // the image; `in` false = outside: zero-fill) into raw slots st[0..3*stride].
-template <bool RIGHT, int FAC = FAC_RUNTIME>
+template <bool RIGHT, int FAC = FAC_RUNTIME, int IN = IN_U16_DEPTH, bool HALF = false>
 __device__ __forceinline__ void issue_raw(const lane& L, int roff, bool in, uint4* st,
                                           int stride) {
     const bool l = in && L.hl, rt = in && L.hr;
+    const bool in2 = HALF ? in && L.full : in;  // second half of a 4-pixel access
     char*      s0 = reinterpret_cast<char*>(st);
     char*      s1 = reinterpret_cast<char*>(st + stride);
-    const unsigned short* a = L.A + roff;
-    const unsigned short* b = L.Bf + roff;
-    cp_async<8>(s0, a, in);
-    cp_async<8>(s0 + 8, b, in);
-    cp_async<4>(s1, a + L.offl, l);
-    cp_async<4>(s1 + 4, b + L.offl, l);
-    if constexpr (RIGHT) {
-        cp_async<4>(s1 + 8, a + L.offr, rt);
-        cp_async<4>(s1 + 12, b + L.offr, rt);
-    }
-    if (has_fac<FAC>(L.fac)) {
-        char*        s3 = reinterpret_cast<char*>(st + 3 * stride);
-        const float* f  = L.fac + roff;
-        cp_async<16>(st + 2 * stride, f, in);
-        cp_async<4>(s3, f + (L.hl ? -1 : 0), l);
-        if constexpr (RIGHT)
-            cp_async<4>(s3 + 4, f + L.offr, rt);
+    if constexpr (IN == IN_F32_RANGE) {
+        char*        s2 = reinterpret_cast<char*>(st + 2 * stride);
+        const float* a  = L.Af + roff;
+        const float* b  = L.Bff + roff;
+        if constexpr (HALF) {
+            cp_async<8>(s0, a, in);
+            cp_async<8>(s0 + 8, a + (L.full ? 2 : 0), in2);
+            cp_async<8>(s1, b, in);
+            cp_async<8>(s1 + 8, b + (L.full ? 2 : 0), in2);
+        } else {
+            cp_async<16>(s0, a, in);
+            cp_async<16>(s1, b, in);
+        }
+        cp_async<4>(s2, a + L.offl, l);
+        cp_async<4>(s2 + 4, b + L.offl, l);
+        if constexpr (RIGHT) {
+            cp_async<4>(s2 + 8, a + L.offr, rt);
+            cp_async<4>(s2 + 12, b + L.offr, rt);
+        }
+        return;
+    } else {
+        const unsigned short* a = L.A + roff;
+        const unsigned short* b = L.Bf + roff;
+        if constexpr (HALF) {
+            cp_async<4>(s0, a, in);
+            cp_async<4>(s0 + 4, a + (L.full ? 2 : 0), in2);
+            cp_async<4>(s0 + 8, b, in);
+            cp_async<4>(s0 + 12, b + (L.full ? 2 : 0), in2);
+        } else {
+            cp_async<8>(s0, a, in);
+            cp_async<8>(s0 + 8, b, in);
+        }
+        cp_async<4>(s1, a + L.offl, l);
+        cp_async<4>(s1 + 4, b + L.offl, l);
+        if constexpr (RIGHT) {
+            cp_async<4>(s1 + 8, a + L.offr, rt);
+            cp_async<4>(s1 + 12, b + L.offr, rt);
+        }
+        if (has_fac<FAC>(L.fac)) {
+            char*        s2 = reinterpret_cast<char*>(st + 2 * stride);
+            char*        s3 = reinterpret_cast<char*>(st + 3 * stride);
+            const float* f  = L.fac + roff;
+            if constexpr (HALF) {
+                cp_async<8>(s2, f, in);
+                cp_async<8>(s2 + 8, f + (L.full ? 2 : 0), in2);
+            } else {
+                cp_async<16>(s2, f, in);
+            }
+            cp_async<4>(s3, f + (L.hl ? -1 : 0), l);
+            if constexpr (RIGHT)
+                cp_async<4>(s3 + 4, f + L.offr, rt);
+        }
     }
 }
 
-template <bool RIGHT, int FAC = FAC_RUNTIME>
+template <bool RIGHT, int FAC = FAC_RUNTIME, int IN = IN_U16_DEPTH>
 __device__ __forceinline__ rawrow fetch_raw(const lane& L, float uniform_factor, const uint4* st,
                                             int stride) {
-    rawrow      x;
-    const uint4 ab = st[0], hl = st[stride];
-    x.a            = make_uint2(ab.x, ab.y);
-    x.b            = make_uint2(ab.z, ab.w);
-    x.la = hl.x, x.lb = hl.y;
-    x.ra = RIGHT ? hl.z : 0u, x.rb = RIGHT ? hl.w : 0u;
-    if (has_fac<FAC>(L.fac)) {
-        x.f             = *reinterpret_cast<const float4*>(st + 2 * stride);
-        const float4 fe = *reinterpret_cast<const float4*>(st + 3 * stride);
-        x.fl = fe.x, x.fr = fe.y;
+    rawrow x;
+    if constexpr (IN == IN_F32_RANGE) {
+        x.fa            = *reinterpret_cast<const float4*>(st);
+        x.fb            = *reinterpret_cast<const float4*>(st + stride);
+        const float4 hl = *reinterpret_cast<const float4*>(st + 2 * stride);
+        x.hla = hl.x, x.hlb = hl.y;
+        x.hra = RIGHT ? hl.z : 0.0f, x.hrb = RIGHT ? hl.w : 0.0f;
+        return x;
     } else {
-        const float v = uniform_factor;
-        x.f           = make_float4(v, v, v, v);
-        x.fl = x.fr = v;
+        const uint4 ab = st[0], hl = st[stride];
+        x.a            = make_uint2(ab.x, ab.y);
+        x.b            = make_uint2(ab.z, ab.w);
+        x.la = hl.x, x.lb = hl.y;
+        x.ra = RIGHT ? hl.z : 0u, x.rb = RIGHT ? hl.w : 0u;
+        if (has_fac<FAC>(L.fac)) {
+            x.f             = *reinterpret_cast<const float4*>(st + 2 * stride);
+            const float4 fe = *reinterpret_cast<const float4*>(st + 3 * stride);
+            x.fl = fe.x, x.fr = fe.y;
+        } else {
+            const float v = uniform_factor;
+            x.f           = make_float4(v, v, v, v);
+            x.fl = x.fr = v;
+        }
+        return x;
     }
-    return x;
 }
+
+// f32 range input: running bounds of the values a thread has loaded, as unsigned
+// bit patterns. hi = max(bits) catches negative values, NaN and infinities too
+// (their patterns exceed every admissible one); lo = min(bits - 1) skips the
+// zeros (0 - 1 wraps to the largest pattern). Raised once, after the strip.
+struct f32_window {
+    unsigned hi = 0u, lo = 0xffffffffu;
+    __device__ __forceinline__ void see(float a, float b) {
+        const unsigned x = __float_as_uint(a), y = __float_as_uint(b);
+        hi = max(hi, max(x, y));
+        lo = min(lo, min(x - 1u, y - 1u));
+    }
+    __device__ __forceinline__ void raise(int* guard) const {
+        if (hi > kF32HiBits || lo < kF32LoBits - 1u)
+            *guard = 1;
+    }
+};
 
 // 2^23 + v as a float has v in its low mantissa bits
 __device__ __forceinline__ float magic_lo(unsigned w) {
@@ -389,24 +469,36 @@ __device__ __forceinline__ float magic_hi(unsigned w) {
 // raw -> range pairs rng[0..5] = columns u0-1 .. u0+4 (conversion/util.h:41-51:
 // float(d) * sqrtf(z); d == 0 gives 0). rng[5] only when RIGHT.
 template <int IN, bool RIGHT>
-__device__ __forceinline__ void to_range(const rawrow& x, f2 (&rng)[6]) {
-    const f2 m = B(-8388608.0f);
-    f2       d[6];
-    d[0] = make_float2(magic_hi(x.la), magic_hi(x.lb));
-    d[1] = make_float2(magic_lo(x.a.x), magic_lo(x.b.x));
-    d[2] = make_float2(magic_hi(x.a.x), magic_hi(x.b.x));
-    d[3] = make_float2(magic_lo(x.a.y), magic_lo(x.b.y));
-    d[4] = make_float2(magic_hi(x.a.y), magic_hi(x.b.y));
-    d[5] = make_float2(magic_lo(x.ra), magic_lo(x.rb));
-    const float fac[6] = {x.fl, x.f.x, x.f.y, x.f.z, x.f.w, x.fr};
+__device__ __forceinline__ void to_range(const rawrow& x, f2 (&rng)[6], f32_window& win) {
+    if constexpr (IN == IN_F32_RANGE) {
+        rng[0] = make_float2(x.hla, x.hlb);
+        rng[1] = make_float2(x.fa.x, x.fb.x);
+        rng[2] = make_float2(x.fa.y, x.fb.y);
+        rng[3] = make_float2(x.fa.z, x.fb.z);
+        rng[4] = make_float2(x.fa.w, x.fb.w);
+        rng[5] = RIGHT ? make_float2(x.hra, x.hrb) : B(0.0f);
 #pragma unroll
-    for (int i = 0; i < (RIGHT ? 6 : 5); ++i) {
-        rng[i] = add2(d[i], m);
-        if constexpr (IN == IN_U16_DEPTH)
-            rng[i] = mul2(rng[i], B(fac[i]));
+        for (int i = 0; i < (RIGHT ? 6 : 5); ++i)
+            win.see(rng[i].x, rng[i].y);
+    } else {
+        const f2 m = B(-8388608.0f);
+        f2       d[6];
+        d[0] = make_float2(magic_hi(x.la), magic_hi(x.lb));
+        d[1] = make_float2(magic_lo(x.a.x), magic_lo(x.b.x));
+        d[2] = make_float2(magic_hi(x.a.x), magic_hi(x.b.x));
+        d[3] = make_float2(magic_lo(x.a.y), magic_lo(x.b.y));
+        d[4] = make_float2(magic_hi(x.a.y), magic_hi(x.b.y));
+        d[5] = make_float2(magic_lo(x.ra), magic_lo(x.rb));
+        const float fac[6] = {x.fl, x.f.x, x.f.y, x.f.z, x.f.w, x.fr};
+#pragma unroll
+        for (int i = 0; i < (RIGHT ? 6 : 5); ++i) {
+            rng[i] = add2(d[i], m);
+            if constexpr (IN == IN_U16_DEPTH)
+                rng[i] = mul2(rng[i], B(fac[i]));
+        }
+        if constexpr (!RIGHT)
+            rng[5] = B(0.0f);
     }
-    if constexpr (!RIGHT)
-        rng[5] = B(0.0f);
 }
 
 __device__ __forceinline__ unsigned short q16(float magic_sum) {
@@ -418,38 +510,68 @@ __device__ __forceinline__ uint2 pack4(float a0, float a1, float a2, float a3) {
 }
 
 // Stores 4 u16 pixels per frame from floats that already hold 1.5*2^23 + value
-// (the integer sits in the low mantissa bits).
-__device__ __forceinline__ void store4_magic(void* base, size_t oa, size_t ob, const f2 (&s)[4]) {
-    unsigned short* o = static_cast<unsigned short*>(base);
-    *reinterpret_cast<uint2*>(o + oa) = pack4(s[0].x, s[1].x, s[2].x, s[3].x);
-    *reinterpret_cast<uint2*>(o + ob) = pack4(s[0].y, s[1].y, s[2].y, s[3].y);
+// (the integer sits in the low mantissa bits). HALF: as two 4-byte stores, the
+// second one only where columns u0+2, u0+3 exist (`full`).
+template <bool HALF = false>
+__device__ __forceinline__ void store4_magic(void* base, size_t oa, size_t ob, const f2 (&s)[4],
+                                             bool full = true) {
+    unsigned short* o  = static_cast<unsigned short*>(base);
+    const uint2     pa = pack4(s[0].x, s[1].x, s[2].x, s[3].x);
+    const uint2     pb = pack4(s[0].y, s[1].y, s[2].y, s[3].y);
+    if constexpr (HALF) {
+        *reinterpret_cast<unsigned*>(o + oa) = pa.x;
+        *reinterpret_cast<unsigned*>(o + ob) = pb.x;
+        if (full) {
+            *reinterpret_cast<unsigned*>(o + oa + 2) = pa.y;
+            *reinterpret_cast<unsigned*>(o + ob + 2) = pb.y;
+        }
+    } else {
+        *reinterpret_cast<uint2*>(o + oa) = pa;
+        *reinterpret_cast<uint2*>(o + ob) = pb;
+    }
 }
 
 // Stores 4 pixels of frame A (.x halves) and frame B (.y halves).
 // OUT_U16: v already holds value * scale; round half to even by the magic add.
-template <int OUT>
-__device__ __forceinline__ void store4(void* base, size_t oa, size_t ob, const f2 (&v)[4]) {
+template <int OUT, bool HALF = false>
+__device__ __forceinline__ void store4(void* base, size_t oa, size_t ob, const f2 (&v)[4],
+                                       bool full = true) {
     if constexpr (OUT == OUT_U16) {
         f2 s[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i)
             s[i] = add2(v[i], B(12582912.0f));
-        unsigned short* o = static_cast<unsigned short*>(base);
-        *reinterpret_cast<uint2*>(o + oa) = pack4(s[0].x, s[1].x, s[2].x, s[3].x);
-        *reinterpret_cast<uint2*>(o + ob) = pack4(s[0].y, s[1].y, s[2].y, s[3].y);
+        store4_magic<HALF>(base, oa, ob, s, full);
     } else {
         float* o = static_cast<float*>(base);
-        *reinterpret_cast<float4*>(o + oa) = make_float4(v[0].x, v[1].x, v[2].x, v[3].x);
-        *reinterpret_cast<float4*>(o + ob) = make_float4(v[0].y, v[1].y, v[2].y, v[3].y);
+        if constexpr (HALF) {
+            *reinterpret_cast<float2*>(o + oa) = make_float2(v[0].x, v[1].x);
+            *reinterpret_cast<float2*>(o + ob) = make_float2(v[0].y, v[1].y);
+            if (full) {
+                *reinterpret_cast<float2*>(o + oa + 2) = make_float2(v[2].x, v[3].x);
+                *reinterpret_cast<float2*>(o + ob + 2) = make_float2(v[2].y, v[3].y);
+            }
+        } else {
+            *reinterpret_cast<float4*>(o + oa) = make_float4(v[0].x, v[1].x, v[2].x, v[3].x);
+            *reinterpret_cast<float4*>(o + ob) = make_float4(v[0].y, v[1].y, v[2].y, v[3].y);
+        }
     }
 }
 
 // per-row camera table values: 4 columns -> one slot; uniform tables are
 // passed by value and need no copy. `off` = row * w + u0 (clamped into the table).
 template <int SPEC = SPEC_GENERIC>
-__device__ __forceinline__ void issue_tab4(const tab_ref& t, int off, bool in, uint4* slot) {
-    if (is_table<SPEC>(t))
-        cp_async<16>(slot, t.p + off, in);
+__device__ __forceinline__ void issue_tab4(const tab_ref& t, int off, bool in, uint4* slot,
+                                           bool full = true) {
+    if (is_table<SPEC>(t)) {
+        if constexpr (SPEC == SPEC_HALF) {
+            char* d = reinterpret_cast<char*>(slot);
+            cp_async<8>(d, t.p + off, in);
+            cp_async<8>(d + 8, t.p + off + (full ? 2 : 0), in && full);
+        } else {
+            cp_async<16>(slot, t.p + off, in);
+        }
+    }
 }
 template <int SPEC = SPEC_GENERIC>
 __device__ __forceinline__ float4 fetch_tab4(const tab_ref& t, const uint4* slot) {

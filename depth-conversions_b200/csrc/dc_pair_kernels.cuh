@@ -33,10 +33,17 @@ constexpr int kPairThreads = 128;
 // One window row: range of columns u0-1 .. u0+4 of both frames, plus (curvature
 // only) the minimum over each 3-column neighbourhood for the "any of the nine
 // depths is zero" test.
+// 1: the squares of a bearing window row are computed once, when the row enters
+// the window (5 FFMA2 per row step instead of 17), and carried with it (20 more
+// live registers). profiles/r2_ab_experiments.md
+#ifndef DC_BEARING_CARRY_SQ
+#define DC_BEARING_CARRY_SQ 0
+#endif
 template <int FEAT>
 struct wrow {
     f2 r[6];
     f2 m3[FEAT == FEAT_CURVATURE ? 4 : 1];
+    f2 s[(FEAT == FEAT_BEARING && DC_BEARING_CARRY_SQ) ? 5 : 1];
 };
 
 template <int FEAT>
@@ -45,18 +52,24 @@ struct feat_traits {
 };
 
 template <int FEAT, int IN>
-__device__ __forceinline__ void commit(const rawrow& raw, wrow<FEAT>& dst) {
-    to_range<IN, feat_traits<FEAT>::right>(raw, dst.r);
+__device__ __forceinline__ void commit(const rawrow& raw, wrow<FEAT>& dst, f32_window& win) {
+    to_range<IN, feat_traits<FEAT>::right>(raw, dst.r, win);
     if constexpr (FEAT == FEAT_CURVATURE) {
 #pragma unroll
         for (int i = 0; i < 4; ++i)
             dst.m3[i] = make_float2(fminf(fminf(dst.r[i].x, dst.r[i + 1].x), dst.r[i + 2].x),
                                     fminf(fminf(dst.r[i].y, dst.r[i + 1].y), dst.r[i + 2].y));
     }
+    if constexpr (FEAT == FEAT_BEARING && DC_BEARING_CARRY_SQ) {
+#pragma unroll
+        for (int i = 0; i < 5; ++i)
+            dst.s[i] = mul2(dst.r[i], dst.r[i]);
+    }
 }
 
 struct pos {
     int    v, u0;
+    bool   full;     // SPEC_HALF: columns u0+2, u0+3 exist (else always true)
     size_t oa, ob;   // element offset of (frame, v, u0) in frame A / B
     float  inside[4];  // 1 for pixels a 3x3 stencil computes, else 0 (border)
 };
@@ -90,7 +103,7 @@ struct tab_slots {
 // into the thread's table slots st[0], st[stride], ... `off` = v * w + u0.
 template <int FEAT, int SPEC>
 __device__ __forceinline__ void issue_tabs(const kparams& p, int v, int off, int u0, uint4* st,
-                                           int stride) {
+                                           int stride, bool full) {
     const int w = p.w, h = p.h;
     if constexpr (FEAT == FEAT_BEARING) {
         const bool in = v < h;
@@ -98,7 +111,7 @@ __device__ __forceinline__ void issue_tabs(const kparams& p, int v, int off, int
 #pragma unroll
         for (int d = 0; d < 4; ++d)
             if (wanted<SPEC>(p.out[d]))
-                issue_tab4<SPEC>(p.cosp[d], off, in, st + d * stride);
+                issue_tab4<SPEC>(p.cosp[d], off, in, st + d * stride, full);
     } else if constexpr (FEAT == FEAT_MAX_CURVE) {
         // depth_to_max_curve.h:113-139: all eight phi() are angles between a
         // pixel and one of its bearing "prior" neighbours (see dc_kernels.cuh):
@@ -107,12 +120,12 @@ __device__ __forceinline__ void issue_tabs(const kparams& p, int v, int off, int
         //   ant1 = phi((u+1,v+1),(u,v)) = D(u+1,v+1) (sic, :136)   ant2 = A(u+1,v-1)
         const bool in = v >= 1 && v < h - 1, more = in && u0 + 4 < w;
         off           = in ? off : w;  // rows off-w .. off+w stay inside the table
-        issue_tab4<SPEC>(p.cosp[0], off, in, st);
-        issue_tab4<SPEC>(p.cosp[1], off, in, st + stride);
-        issue_tab4<SPEC>(p.cosp[1], off + w, in, st + 2 * stride);
-        issue_tab4<SPEC>(p.cosp[2], off, in, st + 3 * stride);
-        issue_tab4<SPEC>(p.cosp[2], off + w, in, st + 4 * stride);
-        issue_tab4<SPEC>(p.cosp[3], off - w, in, st + 5 * stride);
+        issue_tab4<SPEC>(p.cosp[0], off, in, st, full);
+        issue_tab4<SPEC>(p.cosp[1], off, in, st + stride, full);
+        issue_tab4<SPEC>(p.cosp[1], off + w, in, st + 2 * stride, full);
+        issue_tab4<SPEC>(p.cosp[2], off, in, st + 3 * stride, full);
+        issue_tab4<SPEC>(p.cosp[2], off + w, in, st + 4 * stride, full);
+        issue_tab4<SPEC>(p.cosp[3], off - w, in, st + 5 * stride, full);
         char*     e  = reinterpret_cast<char*>(st + 6 * stride);
         const int o4 = more ? 4 : 0;
         issue_tab1<SPEC>(p.cosp[0], off + o4, more, e);
@@ -121,9 +134,9 @@ __device__ __forceinline__ void issue_tabs(const kparams& p, int v, int off, int
     } else if constexpr (FEAT == FEAT_CURVATURE) {
         const bool in = v >= 1 && v < h - 1;
         off           = in ? off : 0;
-        issue_tab4<SPEC>(p.d_phi, off, in, st);
-        issue_tab4<SPEC>(p.d_theta, off, in, st + stride);
-        issue_tab4<SPEC>(p.d_phi_theta, off, in, st + 2 * stride);
+        issue_tab4<SPEC>(p.d_phi, off, in, st, full);
+        issue_tab4<SPEC>(p.d_theta, off, in, st + stride, full);
+        issue_tab4<SPEC>(p.d_phi_theta, off, in, st + 2 * stride, full);
     }
 }
 
@@ -164,7 +177,7 @@ __device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BE
     f2 sm[5];  // squares of the centre row: b*b of every pixel, c*c for horizontal
 #pragma unroll
     for (int i = 0; i < 5; ++i)
-        sm[i] = mul2(mid.r[i], mid.r[i]);
+        sm[i] = DC_BEARING_CARRY_SQ ? mid.s[i] : mul2(mid.r[i], mid.r[i]);
 #pragma unroll
     for (int d = 0; d < 4; ++d) {
         if (!wanted<SPEC>(p.out[d]))
@@ -176,7 +189,9 @@ __device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BE
             const f2 b = mid.r[i + 1], bb = sm[i + 1];
             // prior pixel: hor (u-1,v), ver (u,v-1), dia (u-1,v-1), anti (u-1,v+1)
             const f2   c  = d == 0 ? mid.r[i] : d == 1 ? up.r[i + 1] : d == 2 ? up.r[i] : dn.r[i];
-            const f2   cc = d == 0 ? sm[i] : mul2(c, c);
+            const f2   cc = d == 0 ? sm[i]
+                            : !DC_BEARING_CARRY_SQ ? mul2(c, c)
+                            : d == 1 ? up.s[i + 1] : d == 2 ? up.s[i] : dn.s[i];
             constexpr bool WITH_ACOS = OUT == OUT_U16 && !DC_BEARING_FOLD_Q;
             const bres k  = bearing_core2<WITH_ACOS>(b, c, bb, cc, cs[i]);
             // depth_to_bearing.h:204-207: either depth 0 (or the prior pixel
@@ -213,21 +228,26 @@ __device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BE
 #endif
                 const f2    x   = fma2(k.r, sq, off);
 #endif
+#if DC_ABL & 2
+                o[i] = fma2(k.r, B(Q), B(M));
+                (void)va, (void)vb, (void)x;
+#else
                 o[i]            = make_float2(va ? x.x : M, vb ? x.y : M);
+#endif
             } else {
                 const f2 a = acos_signed2(k.q);
                 o[i]       = make_float2(va ? a.x : 0.0f, vb ? a.y : 0.0f);
             }
         }
         if constexpr (OUT == OUT_U16)
-            store4_magic(p.out[d], at.oa, at.ob, o);
+            store4_magic<SPEC == SPEC_HALF>(p.out[d], at.oa, at.ob, o, at.full);
         else
-            store4<OUT>(p.out[d], at.oa, at.ob, o);
+            store4<OUT, SPEC == SPEC_HALF>(p.out[d], at.oa, at.ob, o, at.full);
     }
 }
 
 // ---- max-curve: conversion/depth_to_max_curve.h:55-153 ---------------------
-template <int OUT>
+template <int OUT, int SPEC>
 __device__ __forceinline__ void max_curve_row(const kparams& p, const wrow<FEAT_MAX_CURVE>& up,
                                               const wrow<FEAT_MAX_CURVE>& mid,
                                               const wrow<FEAT_MAX_CURVE>& dn,
@@ -262,7 +282,7 @@ __device__ __forceinline__ void max_curve_row(const kparams& p, const wrow<FEAT_
         a           = mul2(a, B(at.inside[i]));  // border stays 0 (:101-102)
         o[i]        = OUT == OUT_U16 ? mul2(a, B(p.q_max_curve)) : a;
     }
-    store4<OUT>(p.out[0], at.oa, at.ob, o);
+    store4<OUT, SPEC == SPEC_HALF>(p.out[0], at.oa, at.ob, o, at.full);
     if (p.out[1] != nullptr) {
         // the fused `range` output (converter_laserscan.h.inl:9-10):
         // convertTo(CV_16U) = saturate(round half even); range >= 0
@@ -273,7 +293,7 @@ __device__ __forceinline__ void max_curve_row(const kparams& p, const wrow<FEAT_
             if constexpr (OUT == OUT_U16)
                 r[i] = make_float2(fminf(r[i].x, 65535.0f), fminf(r[i].y, 65535.0f));
         }
-        store4<OUT>(p.out[1], at.oa, at.ob, r);
+        store4<OUT, SPEC == SPEC_HALF>(p.out[1], at.oa, at.ob, r, at.full);
     }
 }
 
@@ -370,9 +390,9 @@ __device__ __forceinline__ void curvature_row(const kparams& p, const wrow<FEAT_
         }
     }
     if (wanted<SPEC>(p.out[0]))
-        store4<OUT>(p.out[0], at.oa, at.ob, g);
+        store4<OUT, SPEC == SPEC_HALF>(p.out[0], at.oa, at.ob, g, at.full);
     if (wanted<SPEC>(p.out[1]))
-        store4<OUT>(p.out[1], at.oa, at.ob, m);
+        store4<OUT, SPEC == SPEC_HALF>(p.out[1], at.oa, at.ob, m, at.full);
 }
 
 // ---------------------------------------------------------------------------
@@ -417,7 +437,7 @@ constexpr size_t pair_smem_bytes() {
 template <int FEAT, int IN, int OUT, int SPEC>
 __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
     pair_kernel(const __grid_constant__ kparams p, int n_frames, int rows_per_strip) {
-    const int       groups_x = p.w >> 2;
+    const int       groups_x = (p.w + 3) >> 2;
     const int       strips   = (p.h + rows_per_strip - 1) / rows_per_strip;
     const long long gid      = (long long)blockIdx.x * kPairThreads + threadIdx.x;
     const int       gx       = int(gid % groups_x);
@@ -435,15 +455,27 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
     const int  u0 = gx * 4, w = p.w, h = p.h;
     const int  v0 = strip * rows_per_strip, v1 = min(v0 + rows_per_strip, h);
     constexpr bool R = feat_traits<FEAT>::right;
-    constexpr int  FC = IN != IN_U16_DEPTH ? FAC_NONE : SPEC != SPEC_GENERIC ? FAC_TABLE : FAC_RUNTIME;
+    constexpr bool HALF = SPEC == SPEC_HALF;
+    constexpr int  FC = IN != IN_U16_DEPTH ? FAC_NONE
+                        : (SPEC == SPEC_TABLES || SPEC == SPEC_UNIFORM) ? FAC_TABLE : FAC_RUNTIME;
     lane L;
-    L.A   = static_cast<const unsigned short*>(p.in) + size_t(fa) * p.frame_px + u0;
-    L.Bf  = static_cast<const unsigned short*>(p.in) + size_t(fb) * p.frame_px + u0;
+    if constexpr (IN == IN_F32_RANGE) {
+        L.Af  = static_cast<const float*>(p.in) + size_t(fa) * p.frame_px + u0;
+        L.Bff = static_cast<const float*>(p.in) + size_t(fb) * p.frame_px + u0;
+        L.A = L.Bf = nullptr;
+    } else {
+        L.A   = static_cast<const unsigned short*>(p.in) + size_t(fa) * p.frame_px + u0;
+        L.Bf  = static_cast<const unsigned short*>(p.in) + size_t(fb) * p.frame_px + u0;
+        L.Af = L.Bff = nullptr;
+    }
     L.fac = (IN == IN_U16_DEPTH && p.range_factor.p != nullptr) ? p.range_factor.p + u0 : nullptr;
     L.hl  = u0 > 0;
     L.hr  = R && (u0 + 4 < w);
-    L.offl = L.hl ? -2 : 0;
+    L.full = !HALF || u0 + 4 <= w;
+    // u16: the 4-byte word that holds column u0-1 starts at u0-2; f32: the pixel itself
+    L.offl = L.hl ? (IN == IN_F32_RANGE ? -1 : -2) : 0;
     L.offr = L.hr ? 4 : 0;
+    f32_window win;
     const float ufac = IN == IN_U16_DEPTH ? p.range_factor.value : 1.0f;
 
     curv_consts cc{1.f, 1.f};
@@ -466,13 +498,13 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
     const int  ro_last = (h - 1) * w;
     auto issue_stage = [&](int r, int ro, uint4* st) {
         const bool in = r < h;
-        issue_raw<R, FC>(L, in ? ro : ro_last, in, st, T);
-        issue_tabs<FEAT, SPEC>(p, r - 1, ro - w + u0, u0, st + kRawSlots * T, T);
+        issue_raw<R, FC, IN, HALF>(L, in ? ro : ro_last, in, st, T);
+        issue_tabs<FEAT, SPEC>(p, r - 1, ro - w + u0, u0, st + kRawSlots * T, T, L.full);
     };
     // the three window rows; they rotate by renaming in the three-stage loop
     wrow<FEAT> w0, w1, w2;
-    issue_raw<R, FC>(L, max(v0 - 1, 0) * w, v0 >= 1, stg0, T);
-    issue_raw<R, FC>(L, v0 * w, true, stg1, T);
+    issue_raw<R, FC, IN, HALF>(L, max(v0 - 1, 0) * w, v0 >= 1, stg0, T);
+    issue_raw<R, FC, IN, HALF>(L, v0 * w, true, stg1, T);
     cp_async_commit();
     if constexpr (STAGES == 3) {
         issue_stage(v0 + 1, (v0 + 1) * w, stg2);
@@ -481,8 +513,8 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
     } else {
         cp_async_wait_all();
     }
-    commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, stg0, T), w0);
-    commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, stg1, T), w1);
+    commit<FEAT, IN>(fetch_raw<R, FC, IN>(L, ufac, stg0, T), w0, win);
+    commit<FEAT, IN>(fetch_raw<R, FC, IN>(L, ufac, stg1, T), w1, win);
     if constexpr (STAGES == 3)
         issue_stage(v0 + 2, (v0 + 2) * w, stg0);
     else
@@ -491,6 +523,7 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
 
     pos at;
     at.u0 = u0;
+    at.full = L.full;
     at.oa = size_t(fa) * p.frame_px + size_t(v0) * w + u0;
     at.ob = size_t(fb) * p.frame_px + size_t(v0) * w + u0;
     float col_in[4];
@@ -508,7 +541,7 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
         if constexpr (FEAT == FEAT_BEARING)
             bearing_row<OUT, SPEC>(p, up, mid, dn, tb, at);
         else if constexpr (FEAT == FEAT_MAX_CURVE)
-            max_curve_row<OUT>(p, up, mid, dn, tb, at);
+            max_curve_row<OUT, SPEC>(p, up, mid, dn, tb, at);
         else if constexpr (FEAT == FEAT_CURVATURE)
             curvature_row<OUT, SPEC>(p, up, mid, dn, tb, at, cc);
         at.oa += w;
@@ -524,7 +557,7 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
         auto step = [&](const wrow<FEAT>& up, const wrow<FEAT>& mid, wrow<FEAT>& dn, uint4* sc,
                         uint4* sf) {
             cp_async_wait_but_one();
-            commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, sc, T), dn);
+            commit<FEAT, IN>(fetch_raw<R, FC, IN>(L, ufac, sc, T), dn, win);
             const rtabs<FEAT> tb = fetch_tabs<FEAT, SPEC>(p, sc + kRawSlots * T, T);
             issue_stage(v + 3, ro, sf);
             cp_async_commit();
@@ -562,11 +595,11 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
             uint4* const s_nxt = cur ? stg0 : stg1;
             cur ^= 1;
             cp_async_wait_all();
-            commit<FEAT, IN>(fetch_raw<R, FC>(L, ufac, s_now, T), w2);
+            commit<FEAT, IN>(fetch_raw<R, FC, IN>(L, ufac, s_now, T), w2, win);
             const rtabs<FEAT> tb = fetch_tabs<FEAT, SPEC>(p, s_now + kRawSlots * T, T);
             const bool in2 = v + 2 < h;
-            issue_raw<R, FC>(L, in2 ? roff + w : roff - w, in2, s_nxt, T);
-            issue_tabs<FEAT, SPEC>(p, v + 1, roff + u0, u0, s_nxt + kRawSlots * T, T);
+            issue_raw<R, FC, IN, HALF>(L, in2 ? roff + w : roff - w, in2, s_nxt, T);
+            issue_tabs<FEAT, SPEC>(p, v + 1, roff + u0, u0, s_nxt + kRawSlots * T, T, L.full);
             cp_async_commit();
             roff += w;
             do_row(w0, w1, w2, tb);
@@ -575,6 +608,8 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
         }
     }
     cp_async_wait_all();
+    if constexpr (IN == IN_F32_RANGE)
+        win.raise(p.guard);
 }
 
 // ===========================================================================
@@ -646,6 +681,15 @@ __device__ __forceinline__ f2 edge_end(f2 x, f2 yc, const edge& e) {
 #define DC_MCE_BLOCKS 2
 #endif
 constexpr int kMceStages = 3;
+// 1: the twelve carried lower-end angles of a step live in shared memory (12
+// conflict-free 8-byte words per thread) instead of registers, so that the kernel
+// fits 168 registers / three CTAs per SM. profiles/r2_ab_experiments.md
+#ifndef DC_MCE_CARRY_SMEM
+#define DC_MCE_CARRY_SMEM 0
+#endif
+#ifndef DC_MCE_SINGLE
+#define DC_MCE_SINGLE 0
+#endif
 // SPEC_TABLES: per-pixel cosine tables (960x540 Kinect). Per stage, next to the
 // raw slots of input row r:
 //   slot 4: V(r, u0..u0+3)   slot 5: D(r, u0..u0+3)   slot 6: H(r-1, u0..u0+3)
@@ -658,7 +702,8 @@ __host__ __device__ constexpr int mce_slots() {
 }
 template <int SPEC>
 constexpr size_t mce_smem_bytes() {
-    return size_t(kMceStages) * mce_slots<SPEC>() * kPairThreads * sizeof(uint4);
+    return size_t(kMceStages) * mce_slots<SPEC>() * kPairThreads * sizeof(uint4) +
+           (DC_MCE_CARRY_SMEM ? size_t(12) * kPairThreads * sizeof(f2) : 0);
 }
 // cosines of one step; SPEC_UNIFORM: every entry is the one scalar
 struct mce_cos {
@@ -688,13 +733,22 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
     const int  v0 = strip * rows_per_strip, v1 = min(v0 + rows_per_strip, h);
     constexpr int FC = IN != IN_U16_DEPTH ? FAC_NONE : FAC_TABLE;
     lane L;
-    L.A   = static_cast<const unsigned short*>(p.in) + size_t(fa) * p.frame_px + u0;
-    L.Bf  = static_cast<const unsigned short*>(p.in) + size_t(fb) * p.frame_px + u0;
+    if constexpr (IN == IN_F32_RANGE) {
+        L.Af  = static_cast<const float*>(p.in) + size_t(fa) * p.frame_px + u0;
+        L.Bff = static_cast<const float*>(p.in) + size_t(fb) * p.frame_px + u0;
+        L.A = L.Bf = nullptr;
+    } else {
+        L.A   = static_cast<const unsigned short*>(p.in) + size_t(fa) * p.frame_px + u0;
+        L.Bf  = static_cast<const unsigned short*>(p.in) + size_t(fb) * p.frame_px + u0;
+        L.Af = L.Bff = nullptr;
+    }
     L.fac = IN == IN_U16_DEPTH ? p.range_factor.p + u0 : nullptr;
     L.hl  = u0 > 0;
     L.hr  = u0 + 4 < w;
-    L.offl = L.hl ? -2 : 0;
+    L.full = true;
+    L.offl = L.hl ? (IN == IN_F32_RANGE ? -1 : -2) : 0;
     L.offr = L.hr ? 4 : 0;
+    f32_window win;
     const float cu = p.cosp[0].value;  // SPEC_UNIFORM: == cosp[1..3].value (checked by the launch code)
 
     // Three staging stages (dc_pair.cuh "Staging"): `sc` is consumed by this
@@ -710,7 +764,7 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
     int           rn = v0 + 1, ro = (v0 + 1) * w;  // next row to fetch and its offset
     auto issue = [&](int r, int roff, uint4* st) {
         const bool in = r >= 0 && r < h;
-        issue_raw<true, FC>(L, in ? roff : ro_last, in, st, T);
+        issue_raw<true, FC, IN>(L, in ? roff : ro_last, in, st, T);
         if constexpr (TAB) {
             // tables of row r (V, D) and of row r-1 (H, A); entries of pixels whose
             // prior neighbour lies outside the image are never used unmasked
@@ -730,7 +784,7 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
     };
     auto consume = [&](wrow_sq& dst, mce_cos& cs) {
         cp_async_wait_but_one();
-        to_range<IN, true>(fetch_raw<true, FC>(L, 1.0f, sc, T), dst.r);
+        to_range<IN, true>(fetch_raw<true, FC, IN>(L, 1.0f, sc, T), dst.r, win);
 #pragma unroll
         for (int i = 0; i < 6; ++i) {
             dst.s[i] = mul2(dst.r[i], dst.r[i]);
@@ -757,7 +811,16 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
     issue(v0 - 1, (v0 - 1) * w, sc);
     issue(v0, v0 * w, sn);
 
-    f2 bv[4], bd[4], ba[4];  // carried: angles at row v towards row v-1 (ver, dia, anti-second)
+    // carried: angles at row v towards row v-1 (ver 0..3, dia 4..7, anti-second 8..11)
+#if DC_MCE_CARRY_SMEM
+    f2* const carry = reinterpret_cast<f2*>(smem + kMceStages * NS * T) + threadIdx.x;
+    auto cget = [&](int k) { return carry[k * T]; };
+    auto cset = [&](int k, f2 x) { carry[k * T] = x; };
+#else
+    f2   cr[12];
+    auto cget = [&](int k) { return cr[k]; };
+    auto cset = [&](int k, f2 x) { cr[k] = x; };
+#endif
     // One step: edges of row `mid` and from `mid` down to `dn`. STORE = false is
     // the strip prologue (mid = row v0-1): only the carried angles are produced.
     pos at;
@@ -807,8 +870,8 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
             const float co = cs_(cs.v[i]);
             const edge  e  = edge_shared<!TAB>(mid.r[c], dn.r[c], mid.s[c], dn.s[c], co);
             if constexpr (STORE)
-                take(i, bv[i], edge_end(mid.r[c], yc(dn, c, co), e));
-            bv[i] = edge_end(dn.r[c], yc(mid, c, co), e);
+                take(i, cget(i), edge_end(mid.r[c], yc(dn, c, co), e));
+            cset(i, edge_end(dn.r[c], yc(mid, c, co), e));
         }
         // diagonal edges (c, v) - (c+1, v+1), c = u0-1 .. u0+3: pixel c looks
         // down-right (forward), pixel c+1 of the next row up-left (carried)
@@ -820,8 +883,8 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
                 const edge  e  = edge_shared<!TAB>(mid.r[c], dn.r[c + 1], mid.s[c], dn.s[c + 1], co);
                 if (c >= 1) {
                     if constexpr (STORE)
-                        take(c - 1, bd[c - 1], edge_end(mid.r[c], yc(dn, c + 1, co), e));
-                    bd[c - 1] = pending;
+                        take(c - 1, cget(4 + c - 1), edge_end(mid.r[c], yc(dn, c + 1, co), e));
+                    cset(4 + c - 1, pending);
                 }
                 if (c <= 3)
                     pending = edge_end(dn.r[c + 1], yc(mid, c, co), e);
@@ -837,20 +900,20 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
                 const edge e = edge_shared<!TAB>(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], cu);
                 if constexpr (STORE)
                     if (c <= 4)
-                        take(c - 1, ba[c - 1], edge_end(mid.r[c], dn.c[c - 1], e));
+                        take(c - 1, cget(8 + c - 1), edge_end(mid.r[c], dn.c[c - 1], e));
                 if (c >= 2)
-                    ba[c - 2] = edge_end(dn.r[c - 1], mid.c[c], e);
+                    cset(8 + c - 2, edge_end(dn.r[c - 1], mid.c[c], e));
             } else {
                 if constexpr (STORE)
                     if (c <= 4) {
                         const float co = cs.d[c];  // D(u + 1, v + 1), u = u0 + c - 1
                         const edge  e  = edge_shared<!TAB>(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], co);
-                        take(c - 1, ba[c - 1], edge_end(mid.r[c], mul2(dn.r[c - 1], B(co)), e));
+                        take(c - 1, cget(8 + c - 1), edge_end(mid.r[c], mul2(dn.r[c - 1], B(co)), e));
                     }
                 if (c >= 2) {
                     const float co = cs.a[c - 2];  // A(u0 + c - 1, v)
                     const edge  e  = edge_shared<!TAB>(dn.r[c - 1], mid.r[c], dn.s[c - 1], mid.s[c], co);
-                    ba[c - 2]      = edge_end(dn.r[c - 1], mul2(mid.r[c], B(co)), e);
+                    cset(8 + c - 2, edge_end(dn.r[c - 1], mul2(mid.r[c], B(co)), e));
                 }
             }
         }
@@ -888,6 +951,18 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
     consume(wa, cs);  // row v0-1
     consume(wb, cs);  // row v0 (+ the tables of the step rows v0-1 / v0)
     step(wa, wb, cs, std::false_type{});
+#if DC_MCE_SINGLE
+    // one instantiation of the step (half the code: the kernel shows instruction-
+    // fetch stalls), the window row handed on by 36 register moves
+#pragma unroll 1
+    for (;;) {
+        wa = wb;
+        consume(wb, cs);  // row v+1
+        step(wa, wb, cs, std::true_type{});
+        if (++v >= v1)
+            break;
+    }
+#else
     for (;;) {
         consume(wa, cs);  // row v+1
         step(wb, wa, cs, std::true_type{});
@@ -898,7 +973,10 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
         if (++v >= v1)
             break;
     }
+#endif
     cp_async_wait_all();
+    if constexpr (IN == IN_F32_RANGE)
+        win.raise(p.guard);
 }
 
 // ===========================================================================
@@ -940,26 +1018,40 @@ constexpr int kFlexSlots = 6;
 // slot 3: [ray_x(u0), ray_x(u0+1) | ray_y(u0), ray_y(u0+1)]
 // slot 4: [ray_z(u0), ray_z(u0+1) | ray_y(u0-1) | ray_y(u0+2)]
 // slot 5: [ray_z(u0-1) | ray_z(u0+2) | - | -]
+// f32 range input (no factor): slot 0: [A(u0), A(u0+1) | B(u0), B(u0+1)],
+// slot 1: [A(u0-1) | B(u0-1) | A(u0+2) | B(u0+2)]; the ray slots as above.
 struct flane {
     const unsigned short *A, *Bf;
+    const float *         Af, *Bff;  // f32 input
     const float *         fac, *rx, *ry, *rz;  // tables at column u0 (fac may be nullptr)
     bool                  hl, hr;
 };
 
+template <int IN>
 __device__ __forceinline__ void flex_issue(const flane& L, int roff, bool in, uint4* st, int T) {
     const bool l = in && L.hl, r = in && L.hr;
     const int  ol = L.hl ? -2 : 0, orr = L.hr ? 2 : 0, ol1 = L.hl ? -1 : 0;
     char *     s0 = reinterpret_cast<char*>(st), *s1 = reinterpret_cast<char*>(st + T),
          *s2 = reinterpret_cast<char*>(st + 2 * T), *s3 = reinterpret_cast<char*>(st + 3 * T),
          *s4 = reinterpret_cast<char*>(st + 4 * T), *s5 = reinterpret_cast<char*>(st + 5 * T);
-    const unsigned short *a = L.A + roff, *b = L.Bf + roff;
-    cp_async<4>(s0, a, in);
-    cp_async<4>(s0 + 4, b, in);
-    cp_async<4>(s0 + 8, a + ol, l);
-    cp_async<4>(s0 + 12, b + ol, l);
-    cp_async<4>(s1, a + orr, r);
-    cp_async<4>(s1 + 4, b + orr, r);
-    if (L.fac != nullptr) {
+    if constexpr (IN == IN_F32_RANGE) {
+        const float *a = L.Af + roff, *b = L.Bff + roff;
+        cp_async<8>(s0, a, in);
+        cp_async<8>(s0 + 8, b, in);
+        cp_async<4>(s1, a + ol1, l);
+        cp_async<4>(s1 + 4, b + ol1, l);
+        cp_async<4>(s1 + 8, a + orr, r);
+        cp_async<4>(s1 + 12, b + orr, r);
+    } else {
+        const unsigned short *a = L.A + roff, *b = L.Bf + roff;
+        cp_async<4>(s0, a, in);
+        cp_async<4>(s0 + 4, b, in);
+        cp_async<4>(s0 + 8, a + ol, l);
+        cp_async<4>(s0 + 12, b + ol, l);
+        cp_async<4>(s1, a + orr, r);
+        cp_async<4>(s1 + 4, b + orr, r);
+    }
+    if (IN == IN_U16_DEPTH && L.fac != nullptr) {
         const float* f = L.fac + roff;
         cp_async<4>(s1 + 8, f + ol1, l);
         cp_async<4>(s1 + 12, f + orr, r);
@@ -980,18 +1072,28 @@ __device__ __forceinline__ void flex_issue(const flane& L, int roff, bool in, ui
 // to_camera (:70-76): P = d * ray for columns u0-1 .. u0+2 of both frames
 template <int IN>
 __device__ __forceinline__ void flex_points(const flane& L, float ufac, const uint4* st, int T,
-                                            v3 (&P)[4]) {
+                                            v3 (&P)[4], f32_window& win) {
     const uint4  q0 = st[0], q1 = st[T];
     const float4 q2 = *reinterpret_cast<const float4*>(st + 2 * T);
     const float4 q3 = *reinterpret_cast<const float4*>(st + 3 * T);
     const float4 q4 = *reinterpret_cast<const float4*>(st + 4 * T);
     const float4 q5 = *reinterpret_cast<const float4*>(st + 5 * T);
     f2           d[4];
-    d[0] = make_float2(magic_hi(q0.z), magic_hi(q0.w));
-    d[1] = make_float2(magic_lo(q0.x), magic_lo(q0.y));
-    d[2] = make_float2(magic_hi(q0.x), magic_hi(q0.y));
-    d[3] = make_float2(magic_lo(q1.x), magic_lo(q1.y));
-    const bool  tab   = L.fac != nullptr;
+    if constexpr (IN == IN_F32_RANGE) {
+        d[0] = make_float2(__uint_as_float(q1.x), __uint_as_float(q1.y));
+        d[1] = make_float2(__uint_as_float(q0.x), __uint_as_float(q0.z));
+        d[2] = make_float2(__uint_as_float(q0.y), __uint_as_float(q0.w));
+        d[3] = make_float2(__uint_as_float(q1.z), __uint_as_float(q1.w));
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            win.see(d[i].x, d[i].y);
+    } else {
+        d[0] = make_float2(magic_hi(q0.z), magic_hi(q0.w));
+        d[1] = make_float2(magic_lo(q0.x), magic_lo(q0.y));
+        d[2] = make_float2(magic_hi(q0.x), magic_hi(q0.y));
+        d[3] = make_float2(magic_lo(q1.x), magic_lo(q1.y));
+    }
+    const bool  tab   = IN == IN_U16_DEPTH && L.fac != nullptr;
     const float fc[4] = {tab ? __uint_as_float(q1.z) : ufac, tab ? q2.x : ufac, tab ? q2.y : ufac,
                          tab ? __uint_as_float(q1.w) : ufac};
     const float rx[4] = {q2.z, q3.x, q3.y, q2.w};
@@ -999,7 +1101,7 @@ __device__ __forceinline__ void flex_points(const flane& L, float ufac, const ui
     const float rz[4] = {q5.x, q4.x, q4.y, q5.y};
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        f2 r = add2(d[i], B(-8388608.0f));
+        f2 r = IN == IN_F32_RANGE ? d[i] : add2(d[i], B(-8388608.0f));
         if constexpr (IN == IN_U16_DEPTH)
             r = mul2(r, B(fc[i]));
         P[i] = {mul2(r, B(rx[i])), mul2(r, B(ry[i])), mul2(r, B(rz[i]))};
@@ -1030,8 +1132,16 @@ __global__ void __launch_bounds__(kPairThreads, DC_FLEX_BLOCKS)
     const int u0 = gx * 2, w = p.w, h = p.h;
     const int v0 = strip * rows_per_strip, v1 = min(v0 + rows_per_strip, h);
     flane     L;
-    L.A   = static_cast<const unsigned short*>(p.in) + size_t(fa) * p.frame_px + u0;
-    L.Bf  = static_cast<const unsigned short*>(p.in) + size_t(fb) * p.frame_px + u0;
+    if constexpr (IN == IN_F32_RANGE) {
+        L.Af  = static_cast<const float*>(p.in) + size_t(fa) * p.frame_px + u0;
+        L.Bff = static_cast<const float*>(p.in) + size_t(fb) * p.frame_px + u0;
+        L.A = L.Bf = nullptr;
+    } else {
+        L.A   = static_cast<const unsigned short*>(p.in) + size_t(fa) * p.frame_px + u0;
+        L.Bf  = static_cast<const unsigned short*>(p.in) + size_t(fb) * p.frame_px + u0;
+        L.Af = L.Bff = nullptr;
+    }
+    f32_window win;
     L.fac = (IN == IN_U16_DEPTH && p.range_factor.p != nullptr) ? p.range_factor.p + u0 : nullptr;
     L.rx  = p.ray_x + u0;
     L.ry  = p.ray_y + u0;
@@ -1051,15 +1161,15 @@ __global__ void __launch_bounds__(kPairThreads, DC_FLEX_BLOCKS)
     uint4* const  stg2 = smem + 2 * kFlexSlots * T + threadIdx.x;
 
     v3 w0[4], w1[4], w2[4];
-    flex_issue(L, max(v0 - 1, 0) * w, v0 >= 1, stg0, T);
-    flex_issue(L, v0 * w, true, stg1, T);
+    flex_issue<IN>(L, max(v0 - 1, 0) * w, v0 >= 1, stg0, T);
+    flex_issue<IN>(L, v0 * w, true, stg1, T);
     cp_async_commit();
-    flex_issue(L, min(v0 + 1, h - 1) * w, v0 + 1 < h, stg2, T);
+    flex_issue<IN>(L, min(v0 + 1, h - 1) * w, v0 + 1 < h, stg2, T);
     cp_async_commit();
     cp_async_wait_but_one();
-    flex_points<IN>(L, ufac, stg0, T, w0);
-    flex_points<IN>(L, ufac, stg1, T, w1);
-    flex_issue(L, min(v0 + 2, h - 1) * w, v0 + 2 < h, stg0, T);
+    flex_points<IN>(L, ufac, stg0, T, w0, win);
+    flex_points<IN>(L, ufac, stg1, T, w1, win);
+    flex_issue<IN>(L, min(v0 + 2, h - 1) * w, v0 + 2 < h, stg0, T);
     cp_async_commit();
 
     using TO         = typename out_elem<OUT>::type;
@@ -1073,9 +1183,9 @@ __global__ void __launch_bounds__(kPairThreads, DC_FLEX_BLOCKS)
 #define DC_FLEX_STEP(UP, MID, DN, SC, SN)                                                      \
     {                                                                                          \
         cp_async_wait_but_one();                                                               \
-        flex_points<IN>(L, ufac, SC, T, DN);                                                   \
+        flex_points<IN>(L, ufac, SC, T, DN, win);                                                   \
         const bool in3 = v + 3 < h;                                                            \
-        flex_issue(L, (in3 ? v + 3 : h - 1) * w, in3, SN, T);                                  \
+        flex_issue<IN>(L, (in3 ? v + 3 : h - 1) * w, in3, SN, T);                                  \
         cp_async_commit();                                                                     \
         const bool rin = v >= 1 && v < h - 1;                                                  \
         f2         f[2];                                                                       \
@@ -1115,6 +1225,8 @@ __global__ void __launch_bounds__(kPairThreads, DC_FLEX_BLOCKS)
     }
 #undef DC_FLEX_STEP
     cp_async_wait_all();
+    if constexpr (IN == IN_F32_RANGE)
+        win.raise(p.guard);
 }
 
 // ===========================================================================

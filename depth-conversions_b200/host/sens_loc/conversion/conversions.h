@@ -10,16 +10,22 @@
 //   * precondition violations (image size != intrinsic size, empty image) throw
 //     std::invalid_argument; the reference's GSL contracts terminate;
 //   * a GPU failure throws sens_loc::gpu::error (the reference cannot fail);
-//   * the par_* variants take no tf::Taskflow: the GPU batches frames instead
-//     of rows. depth_to_*_batch() is the many-frames form the tool uses.
+//   * the par_* variants (pre-sized output image, border pixels left untouched)
+//     need no tf::Taskflow: the three-argument form converts at once; the
+//     four-argument form takes any flow type with emplace() (a tf::Taskflow) and
+//     puts the conversion into it as one task, returned twice as the
+//     (synchronisation, work) pair of the reference.
 #ifndef DCB200_SENS_LOC_CONVERSION_H
 #define DCB200_SENS_LOC_CONVERSION_H
 
 #include "../gpu/context.h"
 #include "../math/image.h"
 
+#include <algorithm>
 #include <optional>
 #include <stdexcept>
+#include <type_traits>
+#include <utility>
 
 namespace sens_loc::conversion {
 
@@ -126,16 +132,108 @@ inline math::image<Real> depth_to_max_curve(const math::image<Real>& depth_image
     return detail::one_output<Real>(DC_MAX_CURVE, 0, depth_image, intrinsic);
 }
 
+// ---- par_* : results into a caller-owned image ----------------------------
+namespace detail {
+/// Copies the region [u0, u1) x [v0, v1) of `src` into `dst`; everything else of
+/// `dst` keeps its content (the reference's par_ loops never touch the border).
+template <typename Real>
+inline void copy_region(const math::image<Real>& src, math::image<Real>& dst, int u0, int u1,
+                        int v0, int v1) {
+    if (u1 <= u0)
+        return;
+    for (int v = v0; v < v1; ++v)
+        std::copy(src.data() + std::size_t(v) * src.w() + u0,
+                  src.data() + std::size_t(v) * src.w() + u1,
+                  dst.data() + std::size_t(v) * dst.w() + u0);
+}
+template <typename A, typename B>
+inline void expect_same_image_size(const A& a, const B& b) {
+    if (a.empty() || a.w() != b.w() || a.h() != b.h())
+        throw std::invalid_argument("conversion: output image size does not match the input");
+}
+template <typename Flow, typename Work>
+inline auto as_task(Flow& flow, Work&& work) {
+    auto task = flow.emplace(std::forward<Work>(work));
+    return std::make_pair(task, task);
+}
+}  // namespace detail
+
+/// depth_to_bearing.h:254-279: writes the pixels direction `Direction` computes
+/// (depth_to_bearing.h:135-178) into `out`; all others keep their value.
+template <direction Direction, typename Real = float, typename Intrinsic>
+inline void par_depth_to_bearing(const math::image<Real>& depth_image, const Intrinsic& intrinsic,
+                                 math::image<Real>& out) {
+    detail::expect_same_image_size(out, depth_image);
+    const math::image<Real> res = depth_to_bearing<Direction, Real>(depth_image, intrinsic);
+    const int w = res.w(), h = res.h();
+    constexpr bool hor = Direction == direction::horizontal, ver = Direction == direction::vertical;
+    constexpr bool anti = Direction == direction::antidiagonal;
+    detail::copy_region(res, out, ver ? 0 : 1, w, (hor || anti) ? 0 : 1, anti ? h - 1 : h);
+}
+template <direction Direction, typename Real = float, typename Intrinsic, typename Flow>
+inline auto par_depth_to_bearing(const math::image<Real>& depth_image, const Intrinsic& intrinsic,
+                                 math::image<Real>& out, Flow& flow) {
+    detail::expect_same_image_size(out, depth_image);
+    return detail::as_task(flow, [&depth_image, &intrinsic, &out] {
+        par_depth_to_bearing<Direction, Real>(depth_image, intrinsic, out);
+    });
+}
+/// depth_to_flexion.h:171-191: interior pixels only.
+template <typename Intrinsic, typename Real = typename Intrinsic::real_type>
+inline void par_depth_to_flexion(const math::image<Real>& depth_image, const Intrinsic& intrinsic,
+                                 math::image<Real>& out) {
+    detail::expect_same_image_size(out, depth_image);
+    const math::image<Real> res = depth_to_flexion(depth_image, intrinsic);
+    detail::copy_region(res, out, 1, res.w() - 1, 1, res.h() - 1);
+}
+template <typename Intrinsic, typename Flow, typename Real = typename Intrinsic::real_type>
+inline auto par_depth_to_flexion(const math::image<Real>& depth_image, const Intrinsic& intrinsic,
+                                 math::image<Real>& out, Flow& flow) {
+    detail::expect_same_image_size(out, depth_image);
+    return detail::as_task(flow, [&depth_image, &intrinsic, &out] {
+        par_depth_to_flexion(depth_image, intrinsic, out);
+    });
+}
+/// depth_to_laserscan.h:100-121: every pixel.
+template <typename Real = float, typename PixelType = ushort, typename Intrinsic>
+inline void par_depth_to_laserscan(const math::image<PixelType>& depth_image,
+                                   const Intrinsic& intrinsic, math::image<Real>& out) {
+    detail::expect_same_image_size(out, depth_image);
+    const math::image<Real> res = depth_to_laserscan<Real, PixelType>(depth_image, intrinsic);
+    detail::copy_region(res, out, 0, res.w(), 0, res.h());
+}
+template <typename Real = float, typename PixelType = ushort, typename Intrinsic, typename Flow>
+inline auto par_depth_to_laserscan(const math::image<PixelType>& depth_image,
+                                   const Intrinsic& intrinsic, math::image<Real>& out, Flow& flow) {
+    detail::expect_same_image_size(out, depth_image);
+    return detail::as_task(flow, [&depth_image, &intrinsic, &out] {
+        par_depth_to_laserscan<Real, PixelType>(depth_image, intrinsic, out);
+    });
+}
+
 // ---- quantisers -----------------------------------------------------------
 namespace detail {
-template <typename Real>
-inline math::image<ushort> quantise(int quant, const math::image<Real>& img,
-                                    const math::image<Real>* mask, Real lo, Real hi) {
+template <typename PixelType>
+constexpr int pixel_kind() {
+    static_assert(std::is_same_v<PixelType, ushort> || std::is_same_v<PixelType, uchar> ||
+                      std::is_same_v<PixelType, schar> || std::is_same_v<PixelType, short>,
+                  "quantised images are 8 or 16 bit integers");
+    return std::is_same_v<PixelType, ushort>  ? DC_PX_U16
+           : std::is_same_v<PixelType, uchar> ? DC_PX_U8
+           : std::is_same_v<PixelType, schar> ? DC_PX_I8
+                                              : DC_PX_I16;
+}
+template <typename PixelType, typename Real>
+inline math::image<PixelType> quantise(int quant, const math::image<Real>& img,
+                                       const math::image<Real>* mask, std::optional<Real> lo,
+                                       std::optional<Real> hi) {
     if (img.empty() || (mask != nullptr && (mask->w() != img.w() || mask->h() != img.h())))
         throw std::invalid_argument("quantiser: empty image or mask of another size");
-    math::image<ushort> out(img.w(), img.h());
-    gpu::context::mine().quantise(quant, img.data(), mask != nullptr ? mask->data() : nullptr,
-                                  img.pixels(), out.data(), lo, hi);
+    math::image<PixelType> out(img.w(), img.h());
+    const double           dlo = lo ? double(*lo) : 0., dhi = hi ? double(*hi) : 0.;
+    gpu::context::mine().quantise(quant, pixel_kind<PixelType>(), img.data(),
+                                  mask != nullptr ? mask->data() : nullptr, img.pixels(),
+                                  out.data(), lo ? &dlo : nullptr, hi ? &dhi : nullptr);
     return out;
 }
 }  // namespace detail
@@ -143,38 +241,35 @@ inline math::image<ushort> quantise(int quant, const math::image<Real>& img,
 /// depth_to_bearing.h:282-301
 template <typename Real = float, typename PixelType = ushort>
 inline math::image<PixelType> convert_bearing(const math::image<Real>& bearing_image) {
-    static_assert(std::is_same_v<PixelType, ushort>);
-    return detail::quantise<Real>(DC_Q_BEARING, bearing_image, nullptr, Real(0), Real(0));
+    return detail::quantise<PixelType, Real>(DC_Q_BEARING, bearing_image, nullptr, Real(0), Real(0));
 }
 /// depth_to_flexion.h:194-215
 template <typename PixelType = ushort, typename Real = float>
 inline math::image<PixelType> convert_flexion(const math::image<Real>& flexion_image) {
-    static_assert(std::is_same_v<PixelType, ushort>);
-    return detail::quantise<Real>(DC_Q_FLEXION, flexion_image, nullptr, Real(0), Real(0));
+    return detail::quantise<PixelType, Real>(DC_Q_FLEXION, flexion_image, nullptr, Real(0), Real(0));
 }
 /// depth_to_max_curve.h:156-176
 template <typename PixelType = ushort, typename Real = float>
 inline math::image<PixelType> convert_max_curve(const math::image<Real>& max_curve_image) {
-    static_assert(std::is_same_v<PixelType, ushort>);
-    return detail::quantise<Real>(DC_Q_MAX_CURVE, max_curve_image, nullptr, Real(0), Real(0));
+    return detail::quantise<PixelType, Real>(DC_Q_MAX_CURVE, max_curve_image, nullptr, Real(0), Real(0));
 }
-/// depth_to_curvature.h:253-283. Both clamps are required here (the tool always
-/// passes them, converter_curvature.h.inl:9-10); the min/max-of-image form is
-/// not provided and throws.
+/// depth_to_curvature.h:253-283. A clamp that is not given is the minimum /
+/// maximum over the whole curvature image (:218-228; a reduction on the device).
+/// 16 bit only: the reference's ushort intermediate re-types the result (:263-275).
 template <typename PixelType = ushort, typename Real = float, typename MaskType = Real>
 inline math::image<PixelType> curvature_to_image(const math::image<Real>&     curvature_img,
                                                  const math::image<MaskType>& depth_image_as_mask,
                                                  std::optional<Real> clamp_min = std::nullopt,
                                                  std::optional<Real> clamp_max = std::nullopt) {
-    static_assert(std::is_same_v<PixelType, ushort> && std::is_same_v<MaskType, Real>);
-    if (!clamp_min || !clamp_max)
-        throw std::invalid_argument("curvature_to_image: both clamps are required on the B200 path");
-    return detail::quantise<Real>(DC_Q_CURVATURE, curvature_img, &depth_image_as_mask, *clamp_min,
-                                  *clamp_max);
+    static_assert(std::is_same_v<PixelType, ushort>);
+    // the mask is "saturate_cast<uchar>(depth) != 0" (:263-264): any arithmetic type
+    const math::image<Real> mask = math::convert<Real>(depth_image_as_mask);
+    return detail::quantise<PixelType, Real>(DC_Q_CURVATURE, curvature_img, &mask, clamp_min,
+                                             clamp_max);
 }
 /// range image -> 16 bit, apps/depth2x/converter_laserscan.h.inl:9-10
 inline math::image<ushort> convert_range(const math::image<float>& range_image) {
-    return detail::quantise<float>(DC_Q_RANGE, range_image, nullptr, 0.f, 0.f);
+    return detail::quantise<ushort, float>(DC_Q_RANGE, range_image, nullptr, 0.f, 0.f);
 }
 
 /// depth_scaling.h:21-31: saturate(round(depth * scale + offset))

@@ -91,13 +91,15 @@ class context {
     void convert_host(const dc_job& job) { check(dc_convert_host(_c, &job)); }
     /// Status instead of an exception (the frame pipeline reports per index).
     int try_convert_host(const dc_job& job) noexcept { return dc_convert_host(_c, &job); }
-    void quantise(int quant, const float* feature, const float* mask, std::size_t n,
-                  std::uint16_t* out, float lo, float hi) {
-        check(dc_quantise_host(_c, quant, feature, mask, n, out, lo, hi));
+    /// The general quantiser (dc_quantise_host_ex): `pixel` a dc_pixel, absent
+    /// clamps (curvature only) are the image's own minimum / maximum.
+    void quantise(int quant, int pixel, const float* feature, const float* mask, std::size_t n,
+                  void* out, const double* lo, const double* hi) {
+        check(dc_quantise_host_ex(_c, quant, pixel, DC_OUT_F32, feature, mask, n, out, lo, hi));
     }
-    void quantise(int quant, const double* feature, const double* mask, std::size_t n,
-                  std::uint16_t* out, double lo, double hi) {
-        check(dc_quantise_host_f64(_c, quant, feature, mask, n, out, lo, hi));
+    void quantise(int quant, int pixel, const double* feature, const double* mask, std::size_t n,
+                  void* out, const double* lo, const double* hi) {
+        check(dc_quantise_host_ex(_c, quant, pixel, DC_OUT_F64, feature, mask, n, out, lo, hi));
     }
     [[nodiscard]] const char* last_error() const noexcept { return dc_last_error(_c); }
     [[nodiscard]] dc_ctx*     raw() noexcept { return _c; }

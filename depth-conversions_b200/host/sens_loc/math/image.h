@@ -7,7 +7,9 @@
 #define DCB200_SENS_LOC_MATH_IMAGE_H
 
 #include <cstddef>
+#include <cmath>
 #include <cstring>
+#include <limits>
 #include <memory>
 #include <stdexcept>
 #include <type_traits>
@@ -85,6 +87,33 @@ class image {
     int                          _w = 0, _h = 0;
     std::shared_ptr<PixelType[]> _px;
 };
+
+/// math/image.h:117-128: cv::Mat::convertTo between pixel types. Integer -> real is
+/// exact; real -> integer rounds half to even and saturates (cv::saturate_cast).
+template <typename TargetType, typename PixelType>
+inline image<TargetType> convert(const image<PixelType>& img) {
+    static_assert(std::is_arithmetic_v<TargetType> && std::is_arithmetic_v<PixelType>);
+    if constexpr (std::is_same_v<TargetType, PixelType>) {
+        return img;
+    } else {
+        if (img.empty())
+            return {};
+        image<TargetType> out(img.w(), img.h());
+        const PixelType*  src = img.data();
+        TargetType*       dst = out.data();
+        for (std::size_t i = 0, n = img.pixels(); i < n; ++i) {
+            if constexpr (std::is_integral_v<TargetType> && std::is_floating_point_v<PixelType>) {
+                const double r  = std::nearbyint(double(src[i]));  // round half to even
+                const double lo = double(std::numeric_limits<TargetType>::min());
+                const double hi = double(std::numeric_limits<TargetType>::max());
+                dst[i] = !(r == r) ? TargetType(lo) : TargetType(r < lo ? lo : (r > hi ? hi : r));
+            } else {
+                dst[i] = TargetType(src[i]);
+            }
+        }
+        return out;
+    }
+}
 
 }  // namespace math
 }  // namespace sens_loc

@@ -205,12 +205,28 @@ typedef enum dc_quant {
 } dc_quant;
 
 /* HOST buffers, synchronous. `mask` is read for DC_Q_CURVATURE only (n_px
- * floats), clamp_lo < clamp_hi likewise. Needs no camera. The unclamped form of
- * curvature_to_image (a global min/max reduction, depth_to_curvature.h:218-228)
- * is never taken by depth2x (converter_curvature.h.inl:9-10) and is not
- * provided: pass both clamps. */
+ * floats), clamp_lo < clamp_hi likewise. Needs no camera. 16 bit output, both
+ * clamps: what depth2x uses (converter_curvature.h.inl:9-10). */
 int dc_quantise_host(dc_ctx* ctx, int quant, const float* feature, const float* mask,
                      size_t n_px, uint16_t* out, float clamp_lo, float clamp_hi);
+
+/* Pixel type of a quantised image: the PixelType template argument of
+ * convert_bearing / convert_flexion / convert_max_curve (scale and offset from
+ * detail::scaling_factor<Real, PixelType>, conversion/util.h:71-79; the reference's
+ * unit tests compare 8 bit images, src/unittest/conversion/
+ * test_conversion_bearing.cpp:78-159). */
+typedef enum dc_pixel { DC_PX_U16 = 0, DC_PX_U8 = 1, DC_PX_I8 = 2, DC_PX_I16 = 3 } dc_pixel;
+
+/* The general quantiser. real_kind: DC_OUT_F32 (feature / mask are float) or
+ * DC_OUT_F64 (double). `out` holds n_px pixels of `pixel` type. clamp_lo / clamp_hi
+ * are read for DC_Q_CURVATURE only and may each be NULL = std::nullopt of
+ * curvature_to_image (conversion/depth_to_curvature.h:85-92): a missing bound is the
+ * minimum / maximum over the whole curvature image (std::minmax_element, :218-228),
+ * found by a reduction on the device. DC_Q_CURVATURE and DC_Q_RANGE produce 16 bit
+ * images only (DC_ERR_UNSUPPORTED otherwise); DC_ERR_INVALID unless lower < upper. */
+int dc_quantise_host_ex(dc_ctx* ctx, int quant, int pixel, int real_kind, const void* feature,
+                        const void* mask, size_t n_px, void* out, const double* clamp_lo,
+                        const double* clamp_hi);
 
 /* The same for Real = double images (convert_bearing<double, ushort> etc.). */
 int dc_quantise_host_f64(dc_ctx* ctx, int quant, const double* feature, const double* mask,
@@ -249,6 +265,17 @@ uint64_t dc_kernel_launches(const dc_ctx* ctx);
  * serves a job depends on the camera (per-pixel or scalar angle tables), the
  * input type, the frame width and buffer alignment. */
 const char* dc_last_kernel(const dc_ctx* ctx);
+
+/* DC_IN_F32_RANGE (what sens_loc::conversion::depth_to_*(math::image<float>) sends,
+ * depth_to_flexion.h:31-33, depth_to_bearing.h:44-49) runs on the same guard-free
+ * frame-pair kernels as u16 input while every non-zero value lies in [2^-10, 2^22]
+ * (the window the exact division / square root sequences are proven for). The
+ * kernels check that on the values they load; a batch that holds anything else
+ * (negative, NaN, infinite, out of the window) is converted again, inside the same
+ * call, by the kernels with the guarded IEEE intrinsics. Returns how many batches of
+ * this context needed that (synchronises the device). Results are identical either
+ * way; this is introspection for tests and benchmarks. */
+uint64_t dc_f32_fallbacks(dc_ctx* ctx);
 
 #ifdef __cplusplus
 }

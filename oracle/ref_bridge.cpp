@@ -34,6 +34,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <optional>
 #include <taskflow/taskflow.hpp>
 #include <thread>
 
@@ -171,6 +172,38 @@ void cli_frame(int f, int in_kind, const uint16_t* depth, const Intrinsic& K,
         store(q, out_u16);
     }
 }
+// Every PixelType instantiation of the bounded quantisers (f: a bearing direction,
+// F_FLEXION or F_MAX_CURVE; pixel: 0 ushort, 1 uchar, 2 schar, 3 short) and
+// curvature_to_image with optional clamps (has_lo / has_hi = 0: std::nullopt, the
+// image's own minimum / maximum, depth_to_curvature.h:218-228).
+template <typename Real, typename Px>
+static int quantise_px_impl(int f, const Real* feat, int w, int h, void* out) {
+    using namespace conversion;
+    const auto in = wrap(feat, w, h);
+    math::image<Px> q = f == F_FLEXION     ? convert_flexion<Px>(in)
+                        : f == F_MAX_CURVE ? convert_max_curve<Px>(in)
+                                           : convert_bearing<Real, Px>(in);
+    store(q, static_cast<Px*>(out));
+    return 0;
+}
+template <typename Real>
+static int quantise_px(int f, int pixel, const Real* feat, int w, int h, void* out) {
+    switch (pixel) {
+    case 1: return quantise_px_impl<Real, uchar>(f, feat, w, h, out);
+    case 2: return quantise_px_impl<Real, schar>(f, feat, w, h, out);
+    case 3: return quantise_px_impl<Real, short>(f, feat, w, h, out);
+    default: return quantise_px_impl<Real, ushort>(f, feat, w, h, out);
+    }
+}
+template <typename Real>
+static int curvature_opt(const Real* feat, const Real* range, int w, int h, int has_lo, double lo,
+                         int has_hi, double hi, uint16_t* out) {
+    const std::optional<Real> a = has_lo ? std::optional<Real>(Real(lo)) : std::nullopt;
+    const std::optional<Real> b = has_hi ? std::optional<Real>(Real(hi)) : std::nullopt;
+    const auto q = conversion::curvature_to_image<ushort>(wrap(feat, w, h), wrap(range, w, h), a, b);
+    store(q, out);
+    return 0;
+}
 }  // namespace
 
 extern "C" {
@@ -208,6 +241,20 @@ int ref_convert_bearing_u8_f32(const float* feat, int w, int h, uint8_t* out) {
     const auto q = conversion::convert_bearing<float, uchar>(wrap(feat, w, h));
     store(q, out);
     return 0;
+}
+int ref_quantise_px_f32(int f, int pixel, const float* feat, int w, int h, void* out) {
+    return quantise_px<float>(f, pixel, feat, w, h, out);
+}
+int ref_quantise_px_f64(int f, int pixel, const double* feat, int w, int h, void* out) {
+    return quantise_px<double>(f, pixel, feat, w, h, out);
+}
+int ref_curvature_to_image_opt_f32(const float* feat, const float* range, int w, int h, int has_lo,
+                                   double lo, int has_hi, double hi, uint16_t* out) {
+    return curvature_opt<float>(feat, range, w, h, has_lo, lo, has_hi, hi, out);
+}
+int ref_curvature_to_image_opt_f64(const double* feat, const double* range, int w, int h,
+                                   int has_lo, double lo, int has_hi, double hi, uint16_t* out) {
+    return curvature_opt<double>(feat, range, w, h, has_lo, lo, has_hi, hi, out);
 }
 float ref_phi_f32(int w, int h, float fx, float fy, float cx, float cy, int u1,
                   int v1, int u2, int v2) {

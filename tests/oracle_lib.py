@@ -198,6 +198,12 @@ class RefLib:
         L.ref_quantise_f64.argtypes = L.ref_quantise_f32.argtypes
         L.ref_convert_bearing_u8_f32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.ref_convert_bearing_u8_f64.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.ref_quantise_px_f32.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.ref_quantise_px_f64.argtypes = L.ref_quantise_px_f32.argtypes
+        L.ref_curvature_to_image_opt_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                                     C.c_int, C.c_double, C.c_int, C.c_double,
+                                                     C.c_void_p]
+        L.ref_curvature_to_image_opt_f64.argtypes = L.ref_curvature_to_image_opt_f32.argtypes
         L.ref_phi_f32.restype = C.c_float
         L.ref_phi_f32.argtypes = [C.c_int, C.c_int] + f4 + [C.c_int] * 4
         L.ref_pixel_to_sphere_f32.argtypes = [C.c_int, C.c_int] + f4 + [C.c_int, C.c_int, C.c_void_p]
@@ -244,6 +250,26 @@ class RefLib:
         out = np.empty(feat.shape, np.uint16)
         fn = self.lib.ref_quantise_f32 if feat.dtype == np.float32 else self.lib.ref_quantise_f64
         fn(f, _ptr(feat), _ptr(rng), feat.shape[1], feat.shape[0], lo, hi, _ptr(out))
+        return out
+
+    def quantise_px(self, f, feat, pixel):
+        """convert_bearing / convert_flexion / convert_max_curve<Real, PixelType>;
+        pixel: 0 ushort, 1 uchar, 2 schar, 3 short."""
+        feat = np.ascontiguousarray(feat)
+        out = np.empty(feat.shape, [np.uint16, np.uint8, np.int8, np.int16][pixel])
+        fn = self.lib.ref_quantise_px_f32 if feat.dtype == np.float32 else self.lib.ref_quantise_px_f64
+        fn(f, pixel, _ptr(feat), feat.shape[1], feat.shape[0], _ptr(out))
+        return out
+
+    def curvature_to_image(self, feat, rng, lo=None, hi=None):
+        """curvature_to_image<ushort> with optional clamps (None = std::nullopt)."""
+        feat = np.ascontiguousarray(feat)
+        rng = np.ascontiguousarray(rng, feat.dtype)
+        out = np.empty(feat.shape, np.uint16)
+        fn = (self.lib.ref_curvature_to_image_opt_f32 if feat.dtype == np.float32
+              else self.lib.ref_curvature_to_image_opt_f64)
+        fn(_ptr(feat), _ptr(rng), feat.shape[1], feat.shape[0], int(lo is not None),
+           float(lo or 0.0), int(hi is not None), float(hi or 0.0), _ptr(out))
         return out
 
     def convert_bearing_u8(self, feat):

@@ -275,7 +275,8 @@ def test_max_curve_shared_edges_small_uniform_cameras(pkg, gpu_ctx, oracle, w, h
 
 def test_kernel_selection_is_reported(pkg, gpu_ctx, oracle):
     """dc_last_kernel: per-pixel angle tables (960x540 Kinect) take the frame-pair
-    kernels with tables, widths that are not a multiple of 4 the scalar kernel."""
+    kernels with tables, even widths that are not a multiple of 4 their half-access
+    form, odd widths the scalar kernel."""
     w, h = 960, 540
     set_k(gpu_ctx, kinect_scaled(w, h))
     frames = np.stack([oracle.synth_depth(0xD2C00002, f, w, h) for f in range(2)])
@@ -290,6 +291,10 @@ def test_kernel_selection_is_reported(pkg, gpu_ctx, oracle):
     set_k(gpu_ctx, kinect_scaled(322, 203))
     small = np.stack([oracle.synth_depth(0xD2C00002, 0, 322, 203)])
     gpu_ctx.convert(pkg.DC_BEARING, small, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16, want=(True,) * 4)
+    assert gpu_ctx.last_kernel == "dc::pr::pair_kernel<SPEC_HALF>"  # even, not a multiple of 4
+    set_k(gpu_ctx, kinect_scaled(61, 37))
+    odd = np.stack([oracle.synth_depth(0xD2C00002, 0, 61, 37)])
+    gpu_ctx.convert(pkg.DC_BEARING, odd, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16, want=(True,) * 4)
     assert gpu_ctx.last_kernel.startswith("dc::feature_kernel")
 
 
