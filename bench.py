@@ -21,6 +21,11 @@ pinhole depth, u16 in -> 4 x u16 out.
               (oracle/_ref: the reference's own headers compiled; else the C
               restatement) on a bounded sample, on the host cores of this box
 
+    sustained the timed region's launches back to back for >= 2.5 s, with the SM
+              clock, power and throttle reasons sampled INSIDE that window
+    configs   (N = 1) the other BASELINE.json configs and the library API's f32 forms,
+              device resident: MPix/s, ms per step, kernel, roofline fraction each
+
 --impl reference times that CPU path alone (rank 0 only under torchrun).
 PyTorch is plumbing here: device buffers, the stream, CUDA events, the
 torch.distributed barrier / max-reduce. The kernels are this repo's.
@@ -61,6 +66,13 @@ WORKLOADS = {
     "range_maxcurve_4096x2160": dict(w=4096, h=2160, feature="max_curve", out="u16", outs=2,
                                      frames=16, ref_features=[0, 8], config=4,
                                      desc="laserscan range fused with max-curve, 4096x2160, u16 -> 2x u16"),
+    # the library API's types: f32 range image in, f32 out
+    "bearing4_f32_960x540": dict(w=960, h=540, feature="bearing", out="f32", outs=4, frames=256,
+                                 inp="f32", ref_features=[1, 2, 3, 4], config=2,
+                                 desc="depth_to_bearing x4 over math::image<float>, 960x540, f32 range -> 4x f32"),
+    "flexion_f32_960x540": dict(w=960, h=540, feature="flexion", out="f32", outs=1, frames=256,
+                                inp="f32", ref_features=[5], config=1,
+                                desc="depth_to_flexion over math::image<float>, 960x540, f32 range -> f32"),
     "range_960x540": dict(w=960, h=540, feature="range", out="u16", outs=1, frames=256,
                           ref_features=[0], config=0,
                           desc="depth2x range, 960x540 pinhole depth, u16 -> u16"),
@@ -84,12 +96,17 @@ def kinect_scaled(w, h):
 
 
 def ncu_traffic(workload):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the workload's
-    kernel, from the committed ncu --set full capture (profiles/r1_traffic.json)."""
-    try:
-        return json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))[workload]["dram_bytes"]
-    except Exception:
-        return None
+    """(dram__bytes_read.sum + dram__bytes_write.sum of one launch of the workload's
+    kernel, where that number comes from): NOT measured in this run -- it needs ncu --
+    but read from the committed summary of the ncu --set full capture of the same
+    command (profiles/r2_traffic.json, else the round-1 file)."""
+    for name in ("r2_traffic.json", "r1_traffic.json"):
+        try:
+            e = json.load(open(os.path.join(ROOT, "profiles", name)))[workload]
+            return e["dram_bytes"], f"profiles/{name}: {e.get('source', '')} [{e.get('kernel', '')}]"
+        except Exception:
+            continue
+    return None, None
 
 
 def measured_peak():
@@ -101,38 +118,54 @@ def measured_peak():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons during the timed region."""
+    """nvidia-smi clocks / throttle reasons / power, time-stamped, every 25 ms; the
+    summary of a window is taken from the samples that fall inside it."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.sw_power_cap,power.draw")
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.samples, self._halt = index, [], threading.Event()
 
     def run(self):
-        while not self._halt.is_set():
-            try:
-                out = subprocess.run(
-                    ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                     "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5)
-                parts = [x.strip() for x in out.stdout.strip().split(",")]
-                if len(parts) >= 6:
-                    self.samples.append(parts)
-            except Exception:
-                pass
-            self._halt.wait(0.05)
+        # one long-lived nvidia-smi in loop mode: a sample every 25 ms without a
+        # process start per sample
+        try:
+            proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "25"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            return
+        self._proc = proc
+        for line in proc.stdout:
+            parts = [x.strip() for x in line.strip().split(",")]
+            if len(parts) >= 7:
+                self.samples.append((time.perf_counter(), parts))
+            if self._halt.is_set():
+                break
 
     def stop(self):
         self._halt.set()
+        try:
+            self._proc.terminate()
+        except Exception:
+            pass
         self.join(timeout=6)
-        sm = [float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit()]
-        mx = [float(s[1]) for s in self.samples if s[1].replace(".", "").isdigit()]
+
+    def summary(self, t0=None, t1=None):
+        sel = [p for t, p in self.samples if (t0 is None or t >= t0) and (t1 is None or t <= t1)]
+        num = lambda v: float(v) if v.replace(".", "").isdigit() else None
+        sm = [num(p[0]) for p in sel if num(p[0]) is not None]
+        mx = [num(p[1]) for p in sel if num(p[1]) is not None]
+        pw = [num(p[6]) for p in sel if num(p[6]) is not None]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for s in self.samples for n, v in zip(names, s[2:6]) if v == "Active"})
+        reasons = sorted({n for p in sel for n, v in zip(names, p[2:6]) if v == "Active"})
         return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_mhz_min": min(sm) if sm else None,
                 "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(self.samples)}
+                "power_w": float(np.median(pw)) if pw else None, "samples": len(sel)}
 
 
 def cpu_reference_run(wl, n_frames, threads=0):
@@ -184,14 +217,14 @@ def run_reference(args, wl):
         t_total += dt
     passes = 1 + len(wl.get("more", []))
     value = args.steps * n_frames * px * passes / t_total / 1e6
-    sample = f"{n_frames} frames/step of {wl['desc']} (8 distinct synthetic frames, cyclic), in memory, no PNG I/O"
+    sample = (f"{n_frames} frames per step (a bounded sample of the workload in `config`: "
+              f"8 distinct synthetic frames, cyclic), in memory, no PNG I/O")
     line = {
         "impl": "reference", "metric": "MPix/s per conversion", "value": value, "unit": "MPix/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * t_total / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "desc": wl["desc"], "frames_per_step": n_frames,
-                   "width": wl["w"], "height": wl["h"]},
+        "config": config_dict(args, wl, args.frames or wl["frames"]),
         "cpu_baseline": {"value": value, "unit": "MPix/s", "cores": workers, "kind": kind,
                          "sample": sample},
         "e2e": {"value": value, "unit": "MPix/s", "h2d_bytes_per_step": 0,
@@ -199,6 +232,138 @@ def run_reference(args, wl):
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def algorithmic_bytes(wl, F):
+    """Each input pixel read once + each output pixel written once."""
+    px = wl["w"] * wl["h"]
+    in_b = 4 if wl.get("inp") == "f32" else 2
+    out_b = 2 if wl["out"] == "u16" else 4
+    total = F * px * (in_b + wl["outs"] * out_b)
+    for _, n in wl.get("more", []):
+        total += F * px * (in_b + n * out_b)
+    return total
+
+
+def config_dict(args, wl, F):
+    """The same dictionary for both arms (--impl ours / reference): the workload."""
+    alg = algorithmic_bytes(wl, F)
+    return {"workload": args.workload, "desc": wl["desc"], "frames_per_step_per_gpu": F,
+            "width": wl["w"], "height": wl["h"], "outputs": wl["outs"], "in_type": wl.get("inp", "u16"),
+            "out_type": wl["out"],
+            "l2": (f"working set per step {alg / 1e6:.0f} MB in+out "
+                   f"{'>' if alg > 126e6 else '<='} 126 MB L2"
+                   + ("; 256 MB L2 flush write between steps" if alg <= 2 * 126e6 else
+                      "; inputs+outputs larger than L2, no flush needed")),
+            "sharding": "frame index, no collective"}
+
+
+class Workload:
+    """Device-resident buffers and jobs of one workload on one GPU."""
+
+    def __init__(self, pkg, torch, dev, local, stream, wl, F, rank, world, sharding):
+        self.pkg, self.torch, self.wl, self.F, self.stream = pkg, torch, wl, F, stream
+        self.sptr = ctypes.c_void_p(stream.cuda_stream)
+        w, h = wl["w"], wl["h"]
+        self.px = w * h
+        k = kinect_scaled(w, h)
+        fmap = {"bearing": pkg.DC_BEARING, "flexion": pkg.DC_FLEXION, "curvature": pkg.DC_CURVATURE,
+                "max_curve": pkg.DC_MAX_CURVE, "range": pkg.DC_RANGE}
+        self.out_kind = pkg.DC_OUT_U16 if wl["out"] == "u16" else pkg.DC_OUT_F32
+        self.out_dtype = torch.uint16 if wl["out"] == "u16" else torch.float32
+        self.extra = wl.get("more", [])
+        self.passes = 1 + len(self.extra)
+        self.features = [wl["feature"]] + [f for f, _ in self.extra]
+        self.ctx = pkg.Context(local)
+        self.ctx.set_pinhole(w, h, k["fx"], k["fy"], k["cx"], k["cy"])
+        frames = sharding.rank_frames(rank, world, F)
+        d_u16 = torch.empty((F, h, w), dtype=torch.uint16, device=dev)
+        self.ctx.synth_depth_device(SEED + wl["config"], frames.start, len(frames), d_u16.data_ptr(), self.sptr)
+        if wl.get("inp") == "f32":
+            # the library API's input: the range image as f32 (depth_to_laserscan of the frames)
+            self.d_in = torch.empty((F, h, w), dtype=torch.float32, device=dev)
+            self.ctx.convert_device(self.ctx.make_job(pkg.DC_RANGE, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_F32, F,
+                                                      d_u16.data_ptr(), [self.d_in.data_ptr()]), self.sptr)
+            torch.cuda.synchronize()
+            del d_u16
+            self.in_kind = pkg.DC_IN_F32_RANGE
+        else:
+            self.d_in, self.in_kind = d_u16, pkg.DC_IN_U16_DEPTH
+        self.d_out = [[torch.empty((F, h, w), dtype=self.out_dtype, device=dev) for _ in range(n)]
+                      for n in [wl["outs"]] + [n for _, n in self.extra]]
+        self.jobs = [self.ctx.make_job(fmap[f], self.in_kind, self.out_kind, F, self.d_in.data_ptr(),
+                                       [o.data_ptr() for o in outs], clamp=(-20.0, 20.0))
+                     for f, outs in zip(self.features, self.d_out)]
+        self.alg_bytes = algorithmic_bytes(wl, F)
+        self.flush = (torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+                      if self.alg_bytes <= 2 * 126e6 else None)
+        self.kernels = []
+
+    def launch_all(self):
+        for j in self.jobs:
+            self.ctx.convert_device(j, self.sptr)
+            if len(self.kernels) < self.passes:
+                self.kernels.append(self.ctx.last_kernel)
+
+    def timed(self, steps, warmup, barrier):
+        """K steps, CUDA events on the launching stream around the kernels of each step
+        (the L2 flush, where one runs, sits between the brackets). Returns the per-step
+        kernel times in ms and the kernel launches counted inside the region."""
+        torch = self.torch
+        for _ in range(warmup):
+            if self.flush is not None:
+                self.flush.fill_(1)
+            self.launch_all()
+        barrier()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+               for _ in range(steps)]
+        launches0 = self.ctx.kernel_launches
+        barrier()
+        t0 = time.perf_counter()
+        for a, b in evs:
+            if self.flush is not None:
+                self.flush.fill_(1)
+            a.record(self.stream)
+            self.launch_all()
+            b.record(self.stream)
+        barrier()
+        wall = time.perf_counter() - t0
+        return [a.elapsed_time(b) for a, b in evs], self.ctx.kernel_launches - launches0, wall, t0
+
+    def sustained(self, seconds):
+        """Back-to-back launches for at least `seconds` (no flush: the batch is larger
+        than L2 or the same flush-free loop a long job runs). One event pair around all."""
+        torch = self.torch
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n, t0 = 0, time.perf_counter()
+        a.record(self.stream)
+        while True:
+            for _ in range(16):
+                self.launch_all()
+            n += 16
+            if time.perf_counter() - t0 >= seconds:
+                break
+            if n % 512 == 0:
+                self.stream.synchronize()  # bound the launch queue
+        b.record(self.stream)
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        return n, a.elapsed_time(b), t0, t1
+
+    def roofline(self, avg_ms, peak, peak_src, name):
+        achieved = self.alg_bytes / (avg_ms * 1e-3) / 1e9
+        traffic, tsrc = ncu_traffic(name)
+        return {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic, "traffic_source": tsrc,
+                "peak_source": peak_src,
+                "kernel": " + ".join(f"{k} [{f}, {self.wl.get('inp', 'u16')} -> {self.wl['out']}]"
+                                     for k, f in zip(self.kernels, self.features)),
+                "launch_ms": avg_ms, "algorithmic_bytes_per_launch": self.alg_bytes,
+                "bytes_per_pixel": self.alg_bytes / (self.F * self.px * self.passes),
+                "passes_per_step": self.passes}
+
+    def close(self):
+        self.ctx.close()
 
 
 def run_ours(args, wl):
@@ -219,30 +384,11 @@ def run_ours(args, wl):
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-
-    w, h, F = wl["w"], wl["h"], args.frames or wl["frames"]
-    px = w * h
-    k = kinect_scaled(w, h)
-    feature = {"bearing": pkg.DC_BEARING, "flexion": pkg.DC_FLEXION,
-               "curvature": pkg.DC_CURVATURE, "max_curve": pkg.DC_MAX_CURVE,
-               "range": pkg.DC_RANGE}[wl["feature"]]
-    out_kind = pkg.DC_OUT_U16 if wl["out"] == "u16" else pkg.DC_OUT_F32
-    out_dtype = torch.uint16 if wl["out"] == "u16" else torch.float32
-    out_b = 2 if wl["out"] == "u16" else 4
-    n_out = wl["outs"]
-    fmap = {"bearing": pkg.DC_BEARING, "flexion": pkg.DC_FLEXION, "curvature": pkg.DC_CURVATURE,
-            "max_curve": pkg.DC_MAX_CURVE, "range": pkg.DC_RANGE}
-    extra = wl.get("more", [])  # further (feature, outputs) passes over the same frames
-    passes = 1 + len(extra)
-
-    ctx = pkg.Context(local)
-    ctx.set_pinhole(w, h, k["fx"], k["fy"], k["cx"], k["cy"])
     # A real (non-NULL) stream: NULL would select the context's own stream and
     # the CUDA events below would not bracket the kernels.
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
     assert stream.cuda_stream != 0
-    sptr = ctypes.c_void_p(stream.cuda_stream)
 
     # frames sharded by frame index, no collective on the data path: rank r owns
     # frames [r*F, (r+1)*F) of every step (depth-conversions_b200/sharding.py)
@@ -251,106 +397,72 @@ def run_ours(args, wl):
         "dc_sharding", os.path.join(ROOT, "depth-conversions_b200", "sharding.py"))
     sharding = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(sharding)
-    my_frames = sharding.rank_frames(rank, world, F)
-    d_in = torch.empty((F, h, w), dtype=torch.uint16, device=dev)
-    d_out = [torch.empty((F, h, w), dtype=out_dtype, device=dev) for _ in range(n_out)]
-    ctx.synth_depth_device(SEED + wl["config"], my_frames.start, len(my_frames), d_in.data_ptr(), sptr)
-    job = ctx.make_job(feature, pkg.DC_IN_U16_DEPTH, out_kind, F, d_in.data_ptr(),
-                       [o.data_ptr() for o in d_out], clamp=(-20.0, 20.0))
-    more_out = [[torch.empty((F, h, w), dtype=out_dtype, device=dev) for _ in range(n)] for _, n in extra]
-    more_jobs = [ctx.make_job(fmap[f], pkg.DC_IN_U16_DEPTH, out_kind, F, d_in.data_ptr(),
-                              [o.data_ptr() for o in outs], clamp=(-20.0, 20.0))
-                 for (f, _), outs in zip(extra, more_out)]
-    alg_bytes = F * px * (2 + n_out * out_b) + sum(F * px * (2 + n * out_b) for _, n in extra)
-    l2_note = (f"working set per step {alg_bytes / 1e6:.0f} MB in+out "
-               f"{'>' if alg_bytes > 126e6 else '<='} 126 MB L2")
-    flush = None
-    if alg_bytes <= 2 * 126e6:
-        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-
-    kernels = []  # kernel family of every pass, as the library reports it (dc_last_kernel)
-
-    def launch_all():
-        ctx.convert_device(job, sptr)
-        if len(kernels) < passes:
-            kernels.append(ctx.last_kernel)
-        for j in more_jobs:
-            ctx.convert_device(j, sptr)
-            if len(kernels) < passes:
-                kernels.append(ctx.last_kernel)
-
-    def step():
-        if flush is not None:
-            flush.fill_(1)
-        launch_all()
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    def max_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    w, h, F = wl["w"], wl["h"], args.frames or wl["frames"]
+    px = w * h
+    W = Workload(pkg, torch, dev, local, stream, wl, F, rank, world, sharding)
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
-    for _ in range(args.warmup):
-        step()
-    barrier()
-    # --- timed region: K steps, CUDA events on the launching stream ----------
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-           for _ in range(args.steps)]
-    launches1 = ctx.kernel_launches
-    barrier()
-    t_wall0 = time.perf_counter()
-    for a, b in evs:
-        if flush is not None:
-            flush.fill_(1)
-        a.record(stream)
-        launch_all()
-        b.record(stream)
-    barrier()
-    t_wall = time.perf_counter() - t_wall0
-    launches_timed = ctx.kernel_launches - launches1
-    kern_ms = [a.elapsed_time(b) for a, b in evs]
-    total_ms = float(sum(kern_ms))
-    if flush is None:
-        # no flush kernels between steps: the wall bracket is the honest step time
-        total_ms = max(total_ms, 0.0)
-    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms = float(t.item())
-    # MPix/s per conversion: input pixels of every pass (a pass = one depth2x sub-command)
-    value = world * args.steps * F * px * passes / (total_ms * 1e-3) / 1e6
 
-    # --- e2e: host buffers through dc_convert_host ---------------------------
-    Fe = min(args.e2e_frames or 128, F)
-    h_in = torch.empty((Fe, h, w), dtype=torch.uint16).pin_memory()
-    h_in.copy_(d_in[:Fe].cpu())
-    h_out = [torch.empty((Fe, h, w), dtype=out_dtype).pin_memory() for _ in range(n_out)]
-    ejob = ctx.make_job(feature, pkg.DC_IN_U16_DEPTH, out_kind, Fe, h_in.data_ptr(),
-                        [o.data_ptr() for o in h_out], clamp=(-20.0, 20.0))
-    more_hout = [[torch.empty((Fe, h, w), dtype=out_dtype).pin_memory() for _ in range(n)] for _, n in extra]
-    ejobs = [ejob] + [ctx.make_job(fmap[f], pkg.DC_IN_U16_DEPTH, out_kind, Fe, h_in.data_ptr(),
-                                   [o.data_ptr() for o in outs], clamp=(-20.0, 20.0))
-                      for (f, _), outs in zip(extra, more_hout)]
-    e_steps = max(3, min(args.steps, 10))
+    # --- the timed region -----------------------------------------------------
+    kern_ms, launches_timed, t_wall, t_region0 = W.timed(args.steps, args.warmup, barrier)
+    t_region1 = time.perf_counter()
+    total_ms = max_over_ranks(float(sum(kern_ms)))
+    # MPix/s per conversion: input pixels of every pass (a pass = one depth2x sub-command)
+    value = world * args.steps * F * px * W.passes / (total_ms * 1e-3) / 1e6
+
+    # --- sustained: the same launches back to back for >= 2 s, clocks sampled inside
+    sustained = None
+    if args.sustain > 0:
+        barrier()
+        n_s, ms_s, ts0, ts1 = W.sustained(args.sustain)
+        ms_s = max_over_ranks(ms_s)
+        sustained = {"seconds": ms_s * 1e-3, "launches": n_s * W.passes,
+                     "value": world * n_s * F * px * W.passes / (ms_s * 1e-3) / 1e6, "unit": "MPix/s",
+                     "ms_per_step": ms_s / n_s, "window": (ts0, ts1)}
+
+    # --- e2e: host buffers through dc_convert_host, the frames and steps of the main leg
+    Fe = min(args.e2e_frames or F, F)
+    out_b = 2 if wl["out"] == "u16" else 4
+    in_b = 4 if wl.get("inp") == "f32" else 2
+    h_in = torch.empty((Fe, h, w), dtype=W.d_in.dtype).pin_memory()
+    h_in.copy_(W.d_in[:Fe].cpu())
+    h_outs = [[torch.empty((Fe, h, w), dtype=W.out_dtype).pin_memory() for _ in outs] for outs in W.d_out]
+    fmap = {"bearing": pkg.DC_BEARING, "flexion": pkg.DC_FLEXION, "curvature": pkg.DC_CURVATURE,
+            "max_curve": pkg.DC_MAX_CURVE, "range": pkg.DC_RANGE}
+    ejobs = [W.ctx.make_job(fmap[f], W.in_kind, W.out_kind, Fe, h_in.data_ptr(),
+                            [o.data_ptr() for o in outs], clamp=(-20.0, 20.0))
+             for f, outs in zip(W.features, h_outs)]
+    e_steps = args.e2e_steps or args.steps
     for _ in range(2):
         for j in ejobs:
-            ctx._check(ctx.convert_host_raw(j))
+            W.ctx._check(W.ctx.convert_host_raw(j))
     barrier()
     t0 = time.perf_counter()
     for _ in range(e_steps):
         for j in ejobs:
-            ctx._check(ctx.convert_host_raw(j))
+            W.ctx._check(W.ctx.convert_host_raw(j))
     torch.cuda.synchronize()
-    e_sec = time.perf_counter() - t0
-    te = torch.tensor([e_sec], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e_value = world * e_steps * Fe * px * passes / float(te.item()) / 1e6
-    clocks = sampler.stop() if sampler else None  # sampled from the warm-up to the end of e2e
+    e_sec = max_over_ranks(time.perf_counter() - t0)
+    e_value = world * e_steps * Fe * px * W.passes / e_sec / 1e6
     # parity spot check of the e2e result against the device-resident result
-    same = all(bool(torch.equal(h_out[i][:1], d_out[i][:1].cpu())) for i in range(n_out))
+    same = all(bool(torch.equal(ho[:1], do[:1].cpu()))
+               for houts, douts in zip(h_outs, W.d_out) for ho, do in zip(houts, douts))
+    n_out_all = sum(len(o) for o in W.d_out)
+    if sampler:
+        sampler.stop()
 
     if rank != 0:
         if world > 1:
@@ -359,39 +471,64 @@ def run_ours(args, wl):
 
     peak, peak_src = measured_peak()
     avg_kernel_ms = float(np.mean(kern_ms))
-    achieved = alg_bytes / (avg_kernel_ms * 1e-3) / 1e9
     line = {
         "metric": "MPix/s per conversion", "value": value, "unit": "MPix/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "desc": wl["desc"], "frames_per_step_per_gpu": F,
-                   "width": w, "height": h, "outputs": n_out, "out_type": wl["out"],
-                   "l2": l2_note + ("; 256 MB L2 flush write between steps" if flush is not None else
-                                    "; inputs+outputs larger than L2, no flush needed"),
-                   "sharding": "frame index, no collective"},
-        "e2e": {"value": e_value, "unit": "MPix/s", "h2d_bytes_per_step": Fe * px * 2 * passes,
-                "d2h_bytes_per_step": Fe * px * (n_out + sum(n for _, n in extra)) * out_b,
-                "frames_per_step_per_gpu": Fe,
-                "steps": e_steps, "api": "dc_convert_host (pinned host buffers)",
-                "matches_device_result": same},
+        "config": config_dict(args, wl, F),
+        "e2e": {"value": e_value, "unit": "MPix/s", "h2d_bytes_per_step": Fe * px * in_b * W.passes,
+                "d2h_bytes_per_step": Fe * px * n_out_all * out_b,
+                "frames_per_step_per_gpu": Fe, "steps": e_steps,
+                "api": "dc_convert_host (pinned host buffers)", "matches_device_result": same},
         "gpu_launches": int(launches_timed),
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": ncu_traffic(args.workload), "peak_source": peak_src,
-                     "kernel": " + ".join(f"{k} [{f}, u16 depth -> {wl['out']}]" for k, f in
-                                          zip(kernels, [wl["feature"]] + [f for f, _ in extra])),
-                     "launch_ms": avg_kernel_ms,
-                     "algorithmic_bytes_per_launch": alg_bytes,
-                     "bytes_per_pixel": alg_bytes / (F * px * passes), "passes_per_step": passes},
-        "clocks": clocks,
+        "roofline": W.roofline(avg_kernel_ms, peak, peak_src, args.workload),
+        # clocks: every nvidia-smi sample (25 ms period) from the first timed step to the end
+        # of the sustained window; the K-step region alone lasts total_ms (often < 25 ms)
+        "clocks": dict(sampler.summary(t_region0, sustained["window"][1] if sustained else t_region1),
+                       timed_region_ms=total_ms),
         "wall_ms_per_step": 1e3 * t_wall / args.steps,
     }
+    if sustained:
+        win = sustained.pop("window")
+        sustained["clocks"] = sampler.summary(*win)
+        sustained["roofline_frac"] = (W.alg_bytes / (sustained["ms_per_step"] * 1e-3) / 1e9) / peak
+        sustained["note"] = ("the timed region's launches repeated back to back without the L2 flush; "
+                             "clocks = nvidia-smi samples inside this window")
+        line["sustained"] = sustained
+    W.close()
+
+    # --- the other BASELINE configs, device resident (N = 1 only): one line for the driver
+    if world == 1 and not args.no_configs:
+        configs = {}
+        names = [n for n in ("flexion_960x540", "bearing4_960x540", "curvature_1920x1080",
+                             "range_maxcurve_4096x2160", "all_1920x1080", "bearing4_f32_960x540",
+                             "flexion_f32_960x540") if n != args.workload]
+        for name in names:
+            wl2 = WORKLOADS[name]
+            X = Workload(pkg, torch, dev, local, stream, wl2, wl2["frames"], 0, 1, sharding)
+            ms, _, _, _ = X.timed(10, 3, barrier)
+            avg = float(np.mean(ms))
+            rf = X.roofline(avg, peak, peak_src, name)
+            configs[name] = {"baseline_config": wl2["config"], "desc": wl2["desc"],
+                             "frames_per_step": wl2["frames"],
+                             "value": wl2["frames"] * wl2["w"] * wl2["h"] * X.passes / (avg * 1e-3) / 1e6,
+                             "unit": "MPix/s", "ms_per_step": avg, "steps": 10, "warmup": 3,
+                             "kernel": rf["kernel"], "bytes_per_pixel": rf["bytes_per_pixel"],
+                             "algorithmic_bytes_per_launch": rf["algorithmic_bytes_per_launch"],
+                             "roofline_frac": rf["frac"], "achieved_gbs": rf["achieved"],
+                             "traffic": rf["traffic"], "traffic_source": rf["traffic_source"],
+                             "l2_flush": X.flush is not None}
+            X.close()
+            del X
+            torch.cuda.empty_cache()
+        line["configs"] = configs
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
         n_cpu = cpu_sample_frames(wl, 12.0, cores)
         dt, workers, kind = cpu_reference_run(wl, n_cpu)
         line["cpu_baseline"] = {
-            "value": n_cpu * px * passes / dt / 1e6, "unit": "MPix/s", "cores": workers, "kind": kind,
+            "value": n_cpu * px * W.passes / dt / 1e6, "unit": "MPix/s", "cores": workers, "kind": kind,
             "sample": f"{n_cpu} frames of the same workload (8 distinct synthetic frames, cyclic), "
                       f"taskflow frame-parallel, in memory, {dt:.1f} s"}
     print(json.dumps(line), flush=True)
@@ -407,7 +544,12 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="bearing4_960x540", choices=sorted(WORKLOADS))
     ap.add_argument("--frames", type=int, default=0, help="frames per step per GPU")
-    ap.add_argument("--e2e-frames", type=int, default=0)
+    ap.add_argument("--e2e-frames", type=int, default=0, help="frames per e2e step (0: as the main leg)")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="e2e steps (0: as the main leg)")
+    ap.add_argument("--sustain", type=float, default=2.5,
+                    help="seconds of back-to-back launches with clocks sampled inside (0: off)")
+    ap.add_argument("--no-configs", action="store_true",
+                    help="skip the device-resident lines of the other BASELINE configs")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)

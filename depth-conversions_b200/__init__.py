@@ -260,7 +260,7 @@ class Context:
         real = DC_OUT_F64 if feature.dtype == np.float64 else DC_OUT_F32
         feature = feature.astype(np.float64 if real == DC_OUT_F64 else np.float32, copy=False)
         m = np.ascontiguousarray(mask, feature.dtype) if mask is not None else None
-        out = np.zeros(feature.shape, _PX_DTYPE[pixel])
+        out = np.zeros(feature.shape, _PX_DTYPE.get(pixel, np.uint16))
         plo = C.byref(C.c_double(lo)) if lo is not None else None
         phi = C.byref(C.c_double(hi)) if hi is not None else None
         rc = self._L.dc_quantise_host_ex(self._h, quant, pixel, real, feature.ctypes.data,

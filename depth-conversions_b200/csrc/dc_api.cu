@@ -355,6 +355,17 @@ int launch_job(dc_ctx* c, const dc_job* j, cudaStream_t s) {
     p.d_phi       = ref_of(c->tabs.d_phi, c->d_curv[0]);
     p.d_theta     = ref_of(c->tabs.d_theta, c->d_curv[1]);
     p.d_phi_theta = ref_of(c->tabs.d_phi_theta, c->d_curv[2]);
+    if (c->tabs.d_phi.uniform && c->tabs.d_theta.uniform && c->tabs.d_phi_theta.uniform) {
+        // math/derivatives.h:66-93: the divisors of the five central differences
+        // (float arithmetic, no contraction: -ffp-contract=off)
+        const volatile float phi = c->tabs.d_phi.value, the = c->tabs.d_theta.value,
+                             pt = c->tabs.d_phi_theta.value;
+        const float b[5] = {2.0f * phi, 2.0f * the, phi * phi, the * the, pt * pt};
+        for (int k = 0; k < 5; ++k) {
+            p.cv_b[k] = b[k];
+            p.cv_y[k] = 1.0f / b[k];
+        }
+    }
     p.lo          = j->clamp_lo;
     p.hi          = j->clamp_hi;
     // conversion/util.h:71-79 scaling_factor<float, ushort>(max_angle) =

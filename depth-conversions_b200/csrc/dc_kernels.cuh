@@ -48,6 +48,12 @@ struct kparams {
     float       q_bearing;    // 65535 / pi
     float       q_max_curve;  // 65535 / (2 pi)
     float       s_scale, s_offset;  // FEAT_SCALE
+    // Curvature with uniform angle tables (dc_pair.cuh SPEC_UNIFORM): the five
+    // camera-only divisors of math/derivatives.h:66-93 -- 2 phi, 2 theta, phi^2,
+    // theta^2, phi_theta^2 -- and their correctly rounded reciprocals, computed once
+    // on the host: as kernel parameters they are uniform operands of the packed
+    // instructions (no register-file read) instead of per-thread registers.
+    float       cv_b[5], cv_y[5];
     // f32 range input on the guard-free kernels: raised (set to 1) by a thread that
     // loads a value outside the window the exact division / square root are proven
     // for (kF32Lo .. kF32Hi, or 0); the IEEE kernel launched behind it then redoes

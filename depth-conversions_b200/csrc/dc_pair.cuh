@@ -35,12 +35,36 @@ __device__ __forceinline__ f2 B(float s) { return make_float2(s, s); }
 __device__ __forceinline__ f2 neg2(f2 a) { return make_float2(-a.x, -a.y); }
 // ptxas 12.9 contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even under
 // --fmad=false (the scalar .rn forms are never contracted), which breaks the
-// reference's rounding order. A product is therefore written as
-// fma(a, b, -0.0) with the -0.0 read from constant memory (opaque to ptxas):
-// RN(a*b + -0) == RN(a*b) for every a, b including signed zeros, the cost is
-// the same FMA-pipe slot, and an FFMA2 result cannot be fused into an add.
+// reference's rounding order. A product is therefore written as an FMA with a
+// zero addend, which cannot be fused into a following add:
+//   mul2(a, b)  = fma(a, b, +0.0): the addend is the zero register (FFMA2 .., RZ),
+//                 no third register read. RN(a*b + +0) == RN(a*b) for every a, b
+//                 EXCEPT that a product of -0 comes out as +0. No result of the
+//                 kernels depends on the sign of an intermediate zero (squares,
+//                 products of ranges >= 0, terms of sums and of |.|), except the
+//                 one product named below.
+//   mul2x(a, b) = fma(a, b, -0.0) with the -0.0 read from constant memory (opaque to
+//                 the compiler, which would fold a literal -0.0 away and then
+//                 contract): exact for every a, b including signed zeros. Costs a
+//                 third operand: a uniform register at best, an ordinary register in
+//                 the unrolled row loops, where ptxas reloads the constant per
+//                 iteration (one more register-file read per product; the register
+//                 file's two reads per clock are what bounds these kernels,
+//                 profiles/r2_rf_roofline.md). Used where the sign of a zero product
+//                 reaches an output: Gaussian curvature's f_uu * f_vv.
+// DC_MUL_NEGZERO=1 restores the -0.0 form everywhere (A/B switch).
+#ifndef DC_MUL_NEGZERO
+#define DC_MUL_NEGZERO 0
+#endif
 static __constant__ float k_neg_zero = -0.0f;  // (one copy per translation unit)
-__device__ __forceinline__ f2 mul2(f2 a, f2 b) { return __ffma2_rn(a, b, make_float2(k_neg_zero, k_neg_zero)); }
+__device__ __forceinline__ f2 mul2x(f2 a, f2 b) { return __ffma2_rn(a, b, make_float2(k_neg_zero, k_neg_zero)); }
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) {
+#if DC_MUL_NEGZERO
+    return mul2x(a, b);
+#else
+    return __ffma2_rn(a, b, make_float2(0.0f, 0.0f));
+#endif
+}
 __device__ __forceinline__ f2 add2(f2 a, f2 b) { return __fadd2_rn(a, b); }
 __device__ __forceinline__ f2 sub2(f2 a, f2 b) { return __fadd2_rn(a, neg2(b)); }
 __device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) { return __ffma2_rn(a, b, c); }

@@ -10,6 +10,17 @@ namespace dc {
 namespace pr {
 
 constexpr int kPairThreads = 128;
+// 1: the row loops that are instantiated several times with renamed registers
+// (curvature, flexion, shared-edge max-curve) have ONE exit, at the bottom: a strip
+// always runs whole groups of steps, steps past the strip's last row only suppress
+// their stores. With an exit after every step ptxas treats the loop as divergent
+// and keeps loop constants that could sit in uniform registers -- above all the
+// -0.0 addend of every product (dc_pair.cuh mul2) -- in ordinary registers: an
+// FFMA2 then reads three register operands instead of two (profiles/r2_ab_experiments.md).
+#ifndef DC_SINGLE_EXIT
+#define DC_SINGLE_EXIT 1
+#endif
+
 #ifndef DC_REFLECT_FSEL
 #define DC_REFLECT_FSEL 1
 #endif
@@ -70,6 +81,7 @@ __device__ __forceinline__ void commit(const rawrow& raw, wrow<FEAT>& dst, f32_w
 struct pos {
     int    v, u0;
     bool   full;     // SPEC_HALF: columns u0+2, u0+3 exist (else always true)
+    bool   live;     // the row belongs to the strip: stores happen (DC_SINGLE_EXIT)
     size_t oa, ob;   // element offset of (frame, v, u0) in frame A / B
     float  inside[4];  // 1 for pixels a 3x3 stencil computes, else 0 (border)
 };
@@ -239,10 +251,12 @@ __device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BE
                 o[i]       = make_float2(va ? a.x : 0.0f, vb ? a.y : 0.0f);
             }
         }
-        if constexpr (OUT == OUT_U16)
-            store4_magic<SPEC == SPEC_HALF>(p.out[d], at.oa, at.ob, o, at.full);
-        else
-            store4<OUT, SPEC == SPEC_HALF>(p.out[d], at.oa, at.ob, o, at.full);
+        if (at.live) {
+            if constexpr (OUT == OUT_U16)
+                store4_magic<SPEC == SPEC_HALF>(p.out[d], at.oa, at.ob, o, at.full);
+            else
+                store4<OUT, SPEC == SPEC_HALF>(p.out[d], at.oa, at.ob, o, at.full);
+        }
     }
 }
 
@@ -282,8 +296,9 @@ __device__ __forceinline__ void max_curve_row(const kparams& p, const wrow<FEAT_
         a           = mul2(a, B(at.inside[i]));  // border stays 0 (:101-102)
         o[i]        = OUT == OUT_U16 ? mul2(a, B(p.q_max_curve)) : a;
     }
-    store4<OUT, SPEC == SPEC_HALF>(p.out[0], at.oa, at.ob, o, at.full);
-    if (p.out[1] != nullptr) {
+    if (at.live)
+        store4<OUT, SPEC == SPEC_HALF>(p.out[0], at.oa, at.ob, o, at.full);
+    if (p.out[1] != nullptr && at.live) {
         // the fused `range` output (converter_laserscan.h.inl:9-10):
         // convertTo(CV_16U) = saturate(round half even); range >= 0
         f2 r[4];
@@ -317,13 +332,22 @@ __device__ __forceinline__ void curvature_row(const kparams& p, const wrow<FEAT_
     for (int i = 0; i < 4; ++i) {
         const int c = i + 1;
         // camera-only divisors, shared by the two frames: scalar
-        const float b_u = mul(2.0f, phi[i]), b_v = mul(2.0f, the[i]);
-        const float b_uu = mul(phi[i], phi[i]), b_vv = mul(the[i], the[i]);
-        const float b_uv = mul(pt[i], pt[i]);
-        const float y_u = rcp_refined(b_u, mufu_rcp(b_u)), y_v = rcp_refined(b_v, mufu_rcp(b_v));
-        const float y_uu = rcp_refined(b_uu, mufu_rcp(b_uu));
-        const float y_vv = rcp_refined(b_vv, mufu_rcp(b_vv));
-        const float y_uv = rcp_refined(b_uv, mufu_rcp(b_uv));
+        float b_u, b_v, b_uu, b_vv, b_uv, y_u, y_v, y_uu, y_vv, y_uv;
+        if constexpr (SPEC == SPEC_UNIFORM) {
+            // host-computed (kparams::cv_b / cv_y): uniform operands. div2 rounds
+            // correctly with any reciprocal as good as the refined MUFU seed; the
+            // host's is the correctly rounded one.
+            b_u = p.cv_b[0], b_v = p.cv_b[1], b_uu = p.cv_b[2], b_vv = p.cv_b[3], b_uv = p.cv_b[4];
+            y_u = p.cv_y[0], y_v = p.cv_y[1], y_uu = p.cv_y[2], y_vv = p.cv_y[3], y_uv = p.cv_y[4];
+        } else {
+            b_u = mul(2.0f, phi[i]), b_v = mul(2.0f, the[i]);
+            b_uu = mul(phi[i], phi[i]), b_vv = mul(the[i], the[i]);
+            b_uv = mul(pt[i], pt[i]);
+            y_u = rcp_refined(b_u, mufu_rcp(b_u)), y_v = rcp_refined(b_v, mufu_rcp(b_v));
+            y_uu = rcp_refined(b_uu, mufu_rcp(b_uu));
+            y_vv = rcp_refined(b_vv, mufu_rcp(b_vv));
+            y_uv = rcp_refined(b_uv, mufu_rcp(b_uv));
+        }
         const f2    left = mid.r[c - 1], right = mid.r[c + 1], upv = up.r[c], down = dn.r[c];
         const f2    two_c = add2(mid.r[c], mid.r[c]);
         const f2    sh = sub2(add2(right, left), two_c);
@@ -341,7 +365,8 @@ __device__ __forceinline__ void curvature_row(const kparams& p, const wrow<FEAT_
         const bool  oka = mna != 0.0f, okb = mnb != 0.0f;
         f2          kg = B(0.0f), km = B(0.0f);
         if (wanted<SPEC>(p.out[0])) {
-            const f2 n = sub2(mul2(f_uu, f_vv), mul2(f_uv, f_uv));
+            // (mul2x: f_uu * f_vv can be -0 and n's sign is the result's, see below)
+            const f2 n = sub2(mul2x(f_uu, f_vv), mul2(f_uv, f_uv));
             kg         = div2_fast(n, dd);
             // n can be -0 (f_uu < 0, f_vv = f_uv = +0); the residual step
             // would turn the quotient into +0. dd > 0: the zero keeps n's sign.
@@ -389,9 +414,9 @@ __device__ __forceinline__ void curvature_row(const kparams& p, const wrow<FEAT_
             m[i] = km;
         }
     }
-    if (wanted<SPEC>(p.out[0]))
+    if (wanted<SPEC>(p.out[0]) && at.live)
         store4<OUT, SPEC == SPEC_HALF>(p.out[0], at.oa, at.ob, g, at.full);
-    if (wanted<SPEC>(p.out[1]))
+    if (wanted<SPEC>(p.out[1]) && at.live)
         store4<OUT, SPEC == SPEC_HALF>(p.out[1], at.oa, at.ob, m, at.full);
 }
 
@@ -524,6 +549,7 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
     pos at;
     at.u0 = u0;
     at.full = L.full;
+    at.live = true;
     at.oa = size_t(fa) * p.frame_px + size_t(v0) * w + u0;
     at.ob = size_t(fb) * p.frame_px + size_t(v0) * w + u0;
     float col_in[4];
@@ -566,6 +592,16 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
             return ++v < v1;
         };
         if constexpr (((DC_PAIR_RENAME_MASK) >> FEAT) & 1) {
+#if DC_SINGLE_EXIT
+            do {
+                at.live = v < v1;
+                step(w0, w1, w2, stg2, stg1);
+                at.live = v < v1;
+                step(w1, w2, w0, stg0, stg2);
+                at.live = v < v1;
+                step(w2, w0, w1, stg1, stg0);
+            } while (v < v1);
+#else
             for (;;) {
                 if (!step(w0, w1, w2, stg2, stg1))
                     break;
@@ -574,6 +610,7 @@ __global__ void __launch_bounds__(kPairThreads, min_blocks<FEAT, SPEC>())
                 if (!step(w2, w0, w1, stg1, stg0))
                     break;
             }
+#endif
         } else {
             uint4 *sc = stg2, *sf = stg1, *sn = stg0;
 #pragma unroll 1
@@ -688,7 +725,7 @@ constexpr int kMceStages = 3;
 #define DC_MCE_CARRY_SMEM 0
 #endif
 #ifndef DC_MCE_SINGLE
-#define DC_MCE_SINGLE 0
+#define DC_MCE_SINGLE 1
 #endif
 // SPEC_TABLES: per-pixel cosine tables (960x540 Kinect). Per stage, next to the
 // raw slots of input row r:
@@ -918,6 +955,7 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
             }
         }
         if constexpr (STORE) {
+            const bool  live   = !DC_SINGLE_EXIT || v < v1;
             const float row_in = (v >= 1 && v < h - 1) ? 1.0f : 0.0f;
             f2          o[4];
 #pragma unroll
@@ -927,8 +965,9 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
                 a    = mul2(a, B(col_in[i] * row_in));  // border stays 0 (:101-102)
                 o[i] = OUT == OUT_U16 ? mul2(a, B(p.q_max_curve)) : a;
             }
-            store4<OUT>(p.out[0], at.oa, at.ob, o);
-            if (p.out[1] != nullptr) {
+            if (live)
+                store4<OUT>(p.out[0], at.oa, at.ob, o);
+            if (p.out[1] != nullptr && live) {
                 // the fused `range` output (converter_laserscan.h.inl:9-10)
                 f2 r[4];
 #pragma unroll
@@ -962,6 +1001,15 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
         if (++v >= v1)
             break;
     }
+#elif DC_SINGLE_EXIT
+    do {
+        consume(wa, cs);  // row v+1
+        step(wb, wa, cs, std::true_type{});
+        ++v;
+        consume(wb, cs);
+        step(wa, wb, cs, std::true_type{});
+        ++v;
+    } while (v < v1);
 #else
     for (;;) {
         consume(wa, cs);  // row v+1
@@ -1202,7 +1250,9 @@ __global__ void __launch_bounds__(kPairThreads, DC_FLEX_BLOCKS)
             f[i] = make_float2(ok ? fminf(fabsf(x.x), 1.0f) : 0.0f,                            \
                                ok ? fminf(fabsf(x.y), 1.0f) : 0.0f);                           \
         }                                                                                      \
-        if constexpr (OUT == OUT_U16) {                                                        \
+        if (DC_SINGLE_EXIT && v >= v1) {                                                       \
+            /* a step past the strip (whole groups of three run): no store */                  \
+        } else if constexpr (OUT == OUT_U16) {                                                 \
             const f2 s0 = add2(mul2(f[0], B(65535.0f)), B(12582912.0f));                       \
             const f2 s1 = add2(mul2(f[1], B(65535.0f)), B(12582912.0f));                       \
             *reinterpret_cast<unsigned*>(out + oa) =                                           \
@@ -1215,14 +1265,15 @@ __global__ void __launch_bounds__(kPairThreads, DC_FLEX_BLOCKS)
         }                                                                                      \
         oa += w;                                                                               \
         ob += w;                                                                               \
-        if (++v >= v1)                                                                         \
+        ++v;                                                                                   \
+        if (!DC_SINGLE_EXIT && v >= v1)                                                        \
             break;                                                                             \
     }
-    for (;;) {
+    do {
         DC_FLEX_STEP(w0, w1, w2, stg2, stg1)
         DC_FLEX_STEP(w1, w2, w0, stg0, stg2)
         DC_FLEX_STEP(w2, w0, w1, stg1, stg0)
-    }
+    } while (v < v1);
 #undef DC_FLEX_STEP
     cp_async_wait_all();
     if constexpr (IN == IN_F32_RANGE)

@@ -170,6 +170,8 @@ struct shared_state {
     }
 };
 
+constexpr std::size_t kMaxFramePixels = std::size_t(1) << 28;  // 16384 x 16384
+
 struct pending_file {
     int                        idx = 0;
     std::vector<unsigned char> bytes;
@@ -180,22 +182,26 @@ struct pending_file {
 // One GPU: indices [first, last] through reader -> gpu -> writer.
 void run_device(const convert_spec& spec, int device, int first, int last, int batch_size,
                 int threads, shared_state& st) {
-    // The context is created before any codec thread starts: cuInit next to 16
-    // threads first-touching their buffers takes 1.3 s instead of 0.6 s (measured;
-    // both sides hammer the address-space lock).
-    dc_ctx* ctx = nullptr;
-    prof("dc_create begin", device);
-    const bool have_ctx = dc_create(device, &ctx) == DC_OK;
-    prof("dc_create end", device);
-    if (!have_ctx) {
-        {
+    // The CUDA context (cuInit + context: 0.4 - 1.5 s of a fresh process, ten times
+    // the pipeline time of a 100-frame job) is created by the GPU thread while the
+    // reader already loads and decodes the first batches: the start-up overlaps the
+    // decode instead of preceding it. DEPTH2X_SERIAL_INIT=1 restores the old order
+    // (context first), which measured faster only when the codec threads' first
+    // touches of large buffers fight cuInit for the address-space lock.
+    static const bool serial_init = std::getenv("DEPTH2X_SERIAL_INIT") != nullptr;
+    dc_ctx*           ctx         = nullptr;
+    bool              have_ctx    = false;
+    auto create_context = [&] {
+        prof("dc_create begin", device);
+        have_ctx = dc_create(device, &ctx) == DC_OK;
+        prof("dc_create end", device);
+        if (!have_ctx) {
             std::lock_guard<std::mutex> l(st.m);
             std::cerr << console::err() << "GPU " << device << ": " << dc_last_error(nullptr) << "\n";
         }
-        for (int i = first; i <= last; ++i)
-            st.fail(i);
-        return;
-    }
+    };
+    if (serial_init)
+        create_context();
     int n_out = 0;
     for (const auto& o : spec.output)
         n_out += !o.empty();
@@ -240,7 +246,11 @@ void run_device(const convert_spec& spec, int device, int first, int last, int b
                     return;
                 if (png::read_file(path, f.bytes, f.hdr) != png::status::ok)
                     return;
-                f.ok = f.hdr.color_type == 0 && f.hdr.bit_depth == 16 && f.hdr.interlace == 0;
+                // (the header is untrusted: a frame beyond 2^28 pixels is refused before
+                // any buffer is sized from it)
+                f.ok = f.hdr.color_type == 0 && f.hdr.bit_depth == 16 && f.hdr.interlace == 0 &&
+                       f.hdr.w > 0 && f.hdr.h > 0 &&
+                       std::size_t(f.hdr.w) * std::size_t(f.hdr.h) <= kMaxFramePixels;
             });
             // frame size of this batch: the intrinsic's (batch_converter.h:152-154),
             // for `scale` the size of the first readable frame; a frame of another
@@ -314,10 +324,14 @@ void run_device(const convert_spec& spec, int device, int first, int last, int b
 
     // ---- gpu -----------------------------------------------------------------
     std::thread gpu([&] {
+        if (!serial_init)
+            create_context();
         int cam_w = -1, cam_h = -1;
         for (;;) {
             batch* b = gpu_q.pop();
-            if (!b->idx.empty()) {
+            if (!have_ctx) {
+                b->gpu_ok = false;  // every index of the batch is reported by the writer
+            } else if (!b->idx.empty()) {
                 int rc = DC_OK;
                 if (spec.camera.model == 0) {
                     if (b->w != cam_w || b->h != cam_h)
@@ -329,7 +343,8 @@ void run_device(const convert_spec& spec, int device, int first, int last, int b
                              : dc_set_equirectangular(ctx, spec.camera.w, spec.camera.h,
                                                       spec.camera.p[0], spec.camera.p[1]);
                 }
-                cam_w = b->w, cam_h = b->h;
+                if (rc == DC_OK)
+                    cam_w = b->w, cam_h = b->h;  // (a failed set is retried by the next batch)
                 if (rc == DC_OK) {
                     dc_job j{};
                     j.feature  = spec.feature;
@@ -404,7 +419,8 @@ void run_device(const convert_spec& spec, int device, int first, int last, int b
     gpu.join();
     writer.join();
     prof("pipeline drained", device);
-    dc_destroy(ctx);
+    if (have_ctx)
+        dc_destroy(ctx);
     prof("context destroyed", device);
 }
 
@@ -435,14 +451,15 @@ run_stats run_batch(const convert_spec& spec, int start, int end, int devices, i
     shared_state             st;
     const auto               t0 = std::chrono::steady_clock::now();
     std::vector<std::thread> workers;
-    const int                per = (total + devices - 1) / devices;
-    for (int g = 0; g < devices; ++g) {
-        const int first = start + g * per, last = std::min(end, first + per - 1);
-        if (first > last)
-            break;
+    // contiguous blocks (sequential file access per GPU), the first total % devices
+    // of them one index longer: every GPU gets work (sharding.py contiguous_blocks)
+    const int base = total / devices, extra = total % devices;
+    for (int g = 0, first = start; g < devices; ++g) {
+        const int n = base + (g < extra ? 1 : 0), last = first + n - 1;
         workers.emplace_back([&, g, first, last] {
             run_device(spec, g, first, last, batch_size, std::max(2, threads / devices), st);
         });
+        first += n;
     }
     for (auto& w : workers)
         w.join();

@@ -114,6 +114,8 @@ status decode_grey(const std::vector<unsigned char>& bytes, const info& hdr, voi
         return status::unsupported;
     const std::size_t bpp = std::size_t(hdr.bit_depth / 8), row = std::size_t(hdr.w) * bpp;
     const std::size_t raw_size = (row + 1) * std::size_t(hdr.h);
+    if (raw_size > std::size_t(0xffffffffu))
+        return status::unsupported;  // zlib's 32-bit counters (uInt avail_out)
     scratch.resize(raw_size);
 
     // Fast path: gather the IDAT payloads (libpng writes 8 KB chunks) and decode the
@@ -163,7 +165,10 @@ status decode_grey(const std::vector<unsigned char>& bytes, const info& hdr, voi
             }
             pos += 12 + len;
         }
-        complete = zs.total_out == raw_size && (zr == Z_STREAM_END || zr == Z_OK);
+        // the whole stream, trailer included: Z_STREAM_END means zlib has verified the
+        // Adler-32 (a cut or trailer-less stream that happens to fill the image is
+        // refused, exactly as the fast path refuses it)
+        complete = zs.total_out == raw_size && zr == Z_STREAM_END;
         inflateEnd(&zs);
     }
     if (!complete)
@@ -231,6 +236,8 @@ status encode_grey(const void* src, int w, int h, int bit_depth, std::vector<uns
         return status::unsupported;
     const std::size_t bpp = std::size_t(bit_depth / 8), row = std::size_t(w) * bpp;
     const std::size_t raw_size = (row + 1) * std::size_t(h);
+    if (raw_size > std::size_t(0x7fffffffu))
+        return status::unsupported;  // one IDAT chunk (31-bit length), zlib's 32-bit counters
     // DC_PNG_ZLIB=1 in the environment: zlib level-1 / Z_RLE (what cv::imwrite
     // produces) instead of the run-length + Huffman encoder of fast_deflate.cpp
     static const bool use_zlib = std::getenv("DC_PNG_ZLIB") != nullptr;

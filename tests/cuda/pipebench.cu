@@ -63,7 +63,7 @@ __device__ __forceinline__ float2 un(u64 v) {
 constexpr int CH = 8;  // independent chains per thread
 
 template <int MODE>
-__global__ void __launch_bounds__(512, 1) bench(float* out, int iters, long long* cyc) {
+__global__ void __launch_bounds__(512, 1) bench(float* out, int iters, long long* cyc, float upar) {
     float x[CH], y[CH], z[CH];
     u64   p[CH], q[CH], r[CH];
     const float s = 1.0f + threadIdx.x * 1e-7f, t = 0.5f;
@@ -77,6 +77,7 @@ __global__ void __launch_bounds__(512, 1) bench(float* out, int iters, long long
         r[i] = pk(y[i] * 0.25f, x[i] * 0.125f);
     }
     const u64 cs = pk(s, s), ct = pk(t, t);
+    const float nzr = out[blockIdx.x * blockDim.x + threadIdx.x];  // loop invariant, per thread (not uniform)
     __syncthreads();
     const long long c0 = clock64();
     for (int it = 0; it < iters; ++it) {
@@ -137,6 +138,15 @@ __global__ void __launch_bounds__(512, 1) bench(float* out, int iters, long long
             if (MODE == 46) { float2 v = __ffma2_rn(un(p[i]), un(q[i]), make_float2(k_nz, k_nz)); p[i] = pk(v.x, v.y);
                               float2 u = __ffma2_rn(un(q[i]), un(r[i]), make_float2(k_nz, k_nz)); q[i] = pk(u.x, u.y);
                               y[i] = fmnmx(y[i], 0.75f); x[i] = fmnmx(x[i], 0.5f); }  // same, the ALU work reads one register each
+            // the addend as a scalar-broadcast REGISTER (c = R.F32): what ptxas emits for the
+            // -0.0 of dc::pr::mul2 inside loops with several exits (flexion, curvature,
+            // shared-edge max-curve), where it does not keep the constant in a uniform register
+            if (MODE == 47) { float2 v = __ffma2_rn(un(p[i]), un(q[i]), make_float2(nzr, nzr)); p[i] = pk(v.x, v.y); }
+            if (MODE == 48) { float2 v = __ffma2_rn(un(p[i]), un(p[i]), make_float2(nzr, nzr)); p[i] = pk(v.x, v.y); }
+            if (MODE == 49) { float2 v = __ffma2_rn(un(p[i]), make_float2(x[i], x[i]), make_float2(nzr, nzr)); p[i] = pk(v.x, v.y); }
+            // division residuals with a camera-only divisor (curvature): the scalar as an
+            // ordinary register (mode 23) against the same scalar as a uniform operand
+            if (MODE == 50) { float2 v = __ffma2_rn(un(p[i]), make_float2(upar, upar), un(r[i])); p[i] = pk(v.x, v.y); }
             if (MODE == 18) { x[i] = rsq(x[i]); y[i] = rsq(y[i]); p[i] = fma2(p[i], cs, ct); q[i] = fma2(q[i], ct, cs); }  // 2 MUFU back to back + 2 FFMA2
         }
     }
@@ -160,13 +170,14 @@ void run(const char* name, int inst_per_chain, int lanes_per_chain, int threads 
     float*     out;
     long long* cyc;
     cudaMalloc(&out, sizeof(float) * blocks * threads);
+    cudaMemset(out, 0, sizeof(float) * blocks * threads);
     cudaMalloc(&cyc, 8);
-    bench<MODE><<<blocks, threads>>>(out, 16, cyc);
+    bench<MODE><<<blocks, threads>>>(out, 16, cyc, 0.999f);
     cudaEvent_t a, b;
     cudaEventCreate(&a);
     cudaEventCreate(&b);
     cudaEventRecord(a);
-    bench<MODE><<<blocks, threads>>>(out, iters, cyc);
+    bench<MODE><<<blocks, threads>>>(out, iters, cyc, 0.999f);
     cudaEventRecord(b);
     cudaDeviceSynchronize();
     float ms;
@@ -226,6 +237,12 @@ int main() {
         run<44>("2 FFMA2(8) + ALU(2)", 3, 4, thr);
         run<45>("2 FFMA2(8) + 2 ALU(4)", 4, 4, thr);
         run<46>("2 FFMA2(8) + 2 ALU(2)", 4, 4, thr);
+        run<47>("FFMA2 a,b distinct c=R.F32", 1, 2, thr);
+        run<48>("FFMA2 square c=R.F32", 1, 2, thr);
+        run<49>("FFMA2 b=R.F32 c=R.F32", 1, 2, thr);
+        run<23>("FFMA2 b=R.F32, a,c pairs", 1, 2, thr);
+        run<50>("FFMA2 b=uniform, a,c pairs", 1, 2, thr);
+        run<19>("FFMA2 a,b,c pairs", 1, 2, thr);
     }
     return 0;
 }

@@ -58,7 +58,9 @@ def test_two_ranks_shard_frames_disjointly():
 
 def test_contiguous_blocks_edge_cases():
     sh = _sharding()
-    assert sh.contiguous_blocks(0, 9, 4) == [(0, 2), (3, 5), (6, 8), (9, 9)]
+    assert sh.contiguous_blocks(0, 9, 4) == [(0, 2), (3, 5), (6, 7), (8, 9)]
+    # every part gets work: 9 frames on 8 GPUs use all 8
+    assert sh.contiguous_blocks(0, 8, 8) == [(0, 1)] + [(i, i) for i in range(2, 9)]
     assert sh.contiguous_blocks(7, 3, 2) == [(3, 5), (6, 7)]      # reversed bounds
     assert sh.contiguous_blocks(5, 5, 8) == [(5, 5)]              # more GPUs than frames
     assert sh.contiguous_blocks(0, 99, 1) == [(0, 99)]
@@ -66,3 +68,5 @@ def test_contiguous_blocks_edge_cases():
         b = sh.contiguous_blocks(0, 9999, parts)
         assert b[0][0] == 0 and b[-1][1] == 9999
         assert all(b[i][1] + 1 == b[i + 1][0] for i in range(len(b) - 1))
+        sizes = [l - f + 1 for f, l in b]
+        assert len(b) == parts and max(sizes) - min(sizes) <= 1

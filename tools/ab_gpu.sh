@@ -6,7 +6,7 @@ WLS=${WLS:-"bearing4_960x540 curvature_1920x1080"}
 mkdir -p gpurun_out
 for lib in $LIBS; do
  for wl in $WLS; do
-  DC_LIB=$PWD/depth-conversions_b200/variants/libdc_$lib.so python bench.py --workload $wl --steps 30 --warmup 3 --no-cpu-baseline ${BENCH_ARGS:-} > gpurun_out/${TAG}_${lib}_$wl.json 2> gpurun_out/${TAG}_${lib}_$wl.err
+  DC_LIB=$PWD/depth-conversions_b200/variants/libdc_$lib.so python bench.py --workload $wl --steps 30 --warmup 3 --no-cpu-baseline --no-configs --sustain 0 ${BENCH_ARGS:-} > gpurun_out/${TAG}_${lib}_$wl.json 2> gpurun_out/${TAG}_${lib}_$wl.err
   python - <<PY
 import json
 try:

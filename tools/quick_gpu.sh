@@ -7,7 +7,7 @@ mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q ${PYTEST_ARGS:-} 2>&1 | tail -15 > gpurun_out/${TAG}_pytest.txt
 cat gpurun_out/${TAG}_pytest.txt
 for wl in $WLS; do
-  python bench.py --workload $wl --steps 20 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_bench_$wl.json 2> gpurun_out/${TAG}_bench_$wl.err
+  python bench.py --workload $wl --steps 20 --warmup 3 --no-cpu-baseline --no-configs --sustain 0 > gpurun_out/${TAG}_bench_$wl.json 2> gpurun_out/${TAG}_bench_$wl.err
   python - <<PY
 import json
 try:
