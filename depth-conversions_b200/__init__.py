@@ -32,8 +32,9 @@ EXPORTED_SYMBOLS = [
     "dc_host_alloc", "dc_host_free", "dc_synth_depth_device", "dc_kernel_launches", "dc_last_kernel",
     "dc_quantise_host", "dc_set_pinhole_f64", "dc_set_equirectangular_f64",
     "dc_quantise_host_f64", "dc_median_host", "dc_median_device", "dc_f32_fallbacks",
-    "dc_quantise_host_ex",
+    "dc_quantise_host_ex", "dc_curvature_to_image_noalloc",
 ]
+DC_NOALLOC_MAX_PIXELS = 1 << 24
 DC_PX_U16, DC_PX_U8, DC_PX_I8, DC_PX_I16 = range(4)
 _PX_DTYPE = {DC_PX_U16: np.uint16, DC_PX_U8: np.uint8, DC_PX_I8: np.int8, DC_PX_I16: np.int16}
 DC_Q_RANGE, DC_Q_BEARING, DC_Q_FLEXION, DC_Q_CURVATURE, DC_Q_MAX_CURVE = range(5)
@@ -105,8 +106,19 @@ def lib():
                                           C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.dc_f32_fallbacks.restype = C.c_uint64
         L.dc_f32_fallbacks.argtypes = [C.c_void_p]
+        L.dc_curvature_to_image_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t,
+                                                    C.c_void_p, C.c_void_p, C.c_char_p, C.c_size_t]
         _lib = L
     return _lib
+
+
+def curvature_to_image_noalloc(device, curvature_ptr, range_ptr, n_px, out_ptr, stream=None):
+    """dc_curvature_to_image_noalloc on DEVICE pointers (ints): -> (status, message).
+    Allocates nothing on the GPU; every call on a GPU shares one fixed scratch."""
+    err = C.create_string_buffer(256)
+    rc = lib().dc_curvature_to_image_noalloc(device, curvature_ptr, range_ptr, n_px, out_ptr,
+                                             stream, err, len(err))
+    return rc, err.value.decode()
 
 
 _IN_DTYPE = {DC_IN_U16_DEPTH: np.uint16, DC_IN_U16_RANGE: np.uint16, DC_IN_F32_RANGE: np.float32,

@@ -228,6 +228,28 @@ int dc_quantise_host_ex(dc_ctx* ctx, int quant, int pixel, int real_kind, const 
                         const void* mask, size_t n_px, void* out, const double* clamp_lo,
                         const double* clamp_hi);
 
+/* curvature_to_image<ushort> WITHOUT clamps (the bounds are the image's own minimum
+ * and maximum, as dc_quantise_host_ex with both clamps NULL) for callers that must
+ * not allocate: code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc. This entry point has NO counterpart in the reference.
+ * It needs no dc_ctx and calls no
+ * cudaMalloc / cudaFree / cudaHostAlloc or allocating library routine: the caller
+ * passes DEVICE buffers on GPU `device` (n_px floats of curvature, n_px floats of
+ * range, n_px 16 bit pixels of result), and the reduction's scratch is a fixed
+ * file-scope __device__ array in the library (33 KB, held by every GPU that loads
+ * the library until exit), which bounds the image: n_px > DC_NOALLOC_MAX_PIXELS is
+ * rejected with DC_ERR_INVALID. Enqueued on `cuda_stream` (NULL = the default
+ * stream), then waits for it; makes `device` the calling thread's current device.
+ * DC_ERR_INVALID with nothing written unless minimum < maximum. On failure a
+ * message is copied into err[0 .. err_len) when err is not NULL.
+ * ALL calls of one process on one GPU share the scratch, which keeps the last
+ * call's contents (each call clears the words that must start at zero): calls that
+ * overlap on the GPU (two streams, two host threads) race on it; serialise them. */
+#define DC_NOALLOC_MAX_PIXELS 16777216u /* 4096 x 4096 */
+int dc_curvature_to_image_noalloc(int device, const float* curvature_device,
+                                  const float* range_device, size_t n_px, uint16_t* out_device,
+                                  void* cuda_stream, char* err, size_t err_len);
+
 /* The same for Real = double images (convert_bearing<double, ushort> etc.). */
 int dc_quantise_host_f64(dc_ctx* ctx, int quant, const double* feature, const double* mask,
                          size_t n_px, uint16_t* out, double clamp_lo, double clamp_hi);
