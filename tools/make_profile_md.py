@@ -1,13 +1,16 @@
 #!/usr/bin/env python
-"""profiles/<tag>_bench_and_ncu.md + profiles/r1_traffic.json from the files
-tools/final_profile.sh left under gpurun_out/."""
+"""profiles/<tag>_bench_and_ncu.md + profiles/<round>_traffic.json (round = the tag's first two
+characters) + profiles/<tag>_sass_hist_<workload>.txt from the files tools/final_profile.sh
+(round 1) / tools/r2_profile.sh left under gpurun_out/."""
 import csv, glob, io, json, os, shutil, subprocess, sys
 tag = sys.argv[1] if len(sys.argv) > 1 else "r1z"
 G = "gpurun_out"
 def last_json(path):
     return json.loads(open(path).read().strip().splitlines()[-1])
-out = [f"# Round 1, final kernels ({tag})", "",
-       "Box: NVIDIA B200, 16 host vCPUs. Produced by `tools/final_profile.sh` (one gpurun call):",
+RND = tag[:2]
+script = "tools/final_profile.sh" if RND == "r1" else "tools/r2_profile.sh"
+out = [f"# Round {RND[1]}, kernels at HEAD ({tag})", "",
+       f"Box: NVIDIA B200, 16 host vCPUs. Produced by `{script}` (one gpurun call):",
        "`python bench.py --workload W --steps 20 --warmup 3 --no-cpu-baseline`, the default `python bench.py`,",
        "`python bench.py --impl reference`, an ncu launch list of the default command and one",
        "`ncu --set full --clock-control none --import-source on -k regex:pair_kernel|stream_kernel|maxcurve_edge_kernel -s 1 -c 1`",
@@ -21,7 +24,7 @@ for f in sorted(glob.glob(f"{G}/{tag}_bench_*.json")):
         continue
     d = last_json(f); r = d["roofline"]; c = d["clocks"]
     out.append(f"| {d['config']['workload']} | {d['value']:.0f} | {d['ms_per_step']:.4f} | {r['achieved']:.0f} | {r['frac']:.3f} "
-               f"| {d['e2e']['value']:.0f} | {c['sm_mhz']:.0f}/{c['sm_max_mhz']:.0f} MHz, reasons {c['reasons']} |")
+               f"| {d['e2e']['value']:.0f} | {c.get('sm_mhz')}/{c.get('sm_max_mhz')} MHz, reasons {c.get('reasons')} |")
 d = last_json(f"{G}/{tag}_bench_default.json"); cb = d["cpu_baseline"]
 out += ["", f"Default line (`python bench.py`, bearing4_960x540): value {d['value']:.0f} MPix/s, e2e {d['e2e']['value']:.0f} MPix/s, "
         f"cpu_baseline {cb['value']:.1f} MPix/s on {cb['cores']} threads (kind {cb['kind']}; {cb['sample']}).",
@@ -37,7 +40,9 @@ want = ['Kernel Name', 'Block Size', 'Grid Size', 'gpu__time_duration.sum', 'dra
         'lts__t_sector_hit_rate.pct', 'lts__throughput.avg.pct_of_peak_sustained_elapsed']
 out.append("## ncu --set full (one launch each)")
 traffic = {}
-for wl in ["bearing4_960x540", "flexion_960x540", "curvature_1920x1080", "range_maxcurve_4096x2160", "maxcurve_960x540", "range_960x540"]:
+WLS = ["bearing4_960x540", "flexion_960x540", "curvature_1920x1080", "range_maxcurve_4096x2160", "maxcurve_960x540", "range_960x540",
+       "bearing4_f32_960x540", "flexion_f32_960x540"]
+for wl in [w for w in WLS if os.path.exists(f"{G}/{tag}_ncu_{w}_raw.csv")]:
     rows = list(csv.reader(io.StringIO(open(f"{G}/{tag}_ncu_{wl}_raw.csv").read())))
     hdr, units, vals = rows[0], rows[1], rows[2]
     def get(k):
@@ -56,12 +61,55 @@ for wl in ["bearing4_960x540", "flexion_960x540", "curvature_1920x1080", "range_
     st = [l for l in s.splitlines() if l.startswith("barrier=")]
     if st:
         out += ["", "stall samples: " + st[0]]
+
+# SASS opcode histogram, pipe-time model and register-read count of each hot loop at this
+# build (the evidence for DESIGN.md section 3's ceilings): profiles/<tag>_sass_hist_<wl>.txt
+import re
+LIB = "depth-conversions_b200/lib/libdepthconv_b200.so"
+STEPS = {"pair_kernel<1": (1, 4), "pair_kernel<3": (3, 4), "pair_kernel<4": (1, 4), "flexion_pair_kernel": (3, 2),
+         "maxcurve_edge_kernel": (1, 4)}
+out += ["", "## SASS histograms of the row loops (tools/sass_hist.py, tools/sass_rf.py on the library of this run)", "",
+        "| workload | kernel | packed FP32 per pixel pair | FMA-pipe clk per row step | issue slots | register reads / 2 | measured clk per row step | measured / largest floor |",
+        "|---|---|---|---|---|---|---|---|"]
+for wl, tr in traffic.items():
+    kn = tr["kernel"]
+    m = re.match(r"void (\w+)<([^>]*)>", kn)
+    if not m or m.group(1) == "stream_kernel":
+        continue
+    key = m.group(1) + "I" + "".join(f"Li{a.strip()}E" for a in m.group(2).split(",")) + "E"
+    steps, pixels = next(v for k, v in STEPS.items() if kn[5:].startswith(k))
+    b = last_json(f"{G}/{tag}_bench_{wl}.json")
+    c = b["config"]
+    fr = c.get("frames_per_step_per_gpu", c.get("frames_per_step"))
+    h = subprocess.run([sys.executable, "tools/sass_hist.py", LIB, key, "--steps", str(steps), "--pixels", str(pixels),
+                        "--ms", f"{b['ms_per_step']:.4f}", "--frames", str(fr), "--w", str(c["width"]), "--h", str(c["height"])],
+                       capture_output=True, text=True).stdout
+    r = subprocess.run([sys.executable, "tools/sass_rf.py", LIB, key, "--steps", str(steps)], capture_output=True, text=True).stdout
+    open(f"profiles/{tag}_sass_hist_{wl}.txt", "w").write(h + "\n" + r)
+    try:
+        packed = float(re.search(r"per pixel pair: ([\d.]+)", h).group(1))
+        pipes = eval(re.search(r"\(one warp\): (\{.*\})", h).group(1))
+        meas = float(re.search(r"\((\d+) clk per row step measured", h).group(1))
+        reads = float(re.search(r"per row step: (\d+) reads", r).group(1))
+        floor = max(pipes["fma"], pipes["issue"], reads / 2)
+        out.append(f"| {wl} | `{kn[5:kn.index('(')]}` | {packed:.1f} | {pipes['fma']:.0f} | {pipes['issue']:.0f} | {reads / 2:.0f} | {meas:.0f} | {meas / floor:.2f} |")
+    except Exception as e:
+        out.append(f"| {wl} | `{kn}` | (parse failed: {e}) | | | | | |")
+if "configs" in d:
+    out += ["", "## The default line's `configs` object (every BASELINE config in one driver-visible run)", "",
+            "| config | workload | MPix/s | ms/step | frac | kernel |", "|---|---|---|---|---|---|"]
+    for name, c in d["configs"].items():
+        out.append(f"| {c.get('baseline_config')} | {name} | {c['value']:.0f} | {c['ms_per_step']:.4f} | {c['roofline_frac']:.3f} | {c['kernel']} |")
+if "sustained" in d:
+    out += ["", "`sustained`: " + json.dumps(d["sustained"])]
 out += ["", "Reading: the stencil kernels are bound by FP32 work (register-file operand bandwidth, DESIGN.md section 3),",
         "not by HBM: DRAM throughput 8-40 %, DRAM traffic = the algorithmic bytes (tables from L2, halos from L1).",
         "The streaming range kernel is HBM bound."]
 open(f"profiles/{tag}_bench_and_ncu.md", "w").write("\n".join(out) + "\n")
-json.dump(traffic, open("profiles/r1_traffic.json", "w"), indent=1)
-shutil.copy(f"{G}/{tag}_launches_bearing4.csv", f"profiles/{tag}_launches_bearing4_960x540.csv")
+json.dump(traffic, open(f"profiles/{RND}_traffic.json", "w"), indent=1)
+for cand in (f"{G}/{tag}_launches_bearing4.csv", f"{G}/{tag}_launches_bearing4_960x540.csv"):
+    if os.path.exists(cand):
+        shutil.copy(cand, f"profiles/{tag}_launches_bearing4_960x540.csv")
 print("\n".join(out[8:24]))
 for k, v in traffic.items():
     print(k, round(v["dram_bytes"] / v["algorithmic_bytes"], 3))
