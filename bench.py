@@ -109,6 +109,19 @@ def ncu_traffic(workload):
     return None, None
 
 
+def box_dma_ceiling(n_gpus, h2d, d2h):
+    """Host<->device copy ceiling of the box with n_gpus GPUs copying at once, from the
+    committed probe (profiles/r2_pcie_probe.json; NOT measured in this run): the
+    bearing-like 1:4 mix when both directions carry data, else the one-direction row."""
+    try:
+        e = json.load(open(os.path.join(ROOT, "profiles", "r2_pcie_probe.json")))
+        row = e["gpus"][str(n_gpus)]
+        key = "h2d+d2h(1:4)" if h2d and d2h else ("h2d" if h2d else "d2h")
+        return row[key], f"profiles/r2_pcie_probe.json [{key}, {n_gpus} GPU(s) active]"
+    except Exception:
+        return None, None
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -489,6 +502,12 @@ def run_ours(args, wl):
                        timed_region_ms=total_ms),
         "wall_ms_per_step": 1e3 * t_wall / args.steps,
     }
+    # e2e against what the box's host<->device DMA delivers to n GPUs copying together
+    e = line["e2e"]
+    dma, dma_src = box_dma_ceiling(world, e["h2d_bytes_per_step"], e["d2h_bytes_per_step"])
+    if dma:
+        moved = world * e_steps * (e["h2d_bytes_per_step"] + e["d2h_bytes_per_step"]) / e_sec / 1e9
+        e.update(moved_gbs=moved, box_dma_gbs=dma, frac_of_box_dma=moved / dma, box_dma_source=dma_src)
     if sustained:
         win = sustained.pop("window")
         sustained["clocks"] = sampler.summary(*win)
