@@ -33,6 +33,7 @@ EXPORTED_SYMBOLS = [
     "dc_quantise_host", "dc_set_pinhole_f64", "dc_set_equirectangular_f64",
     "dc_quantise_host_f64", "dc_median_host", "dc_median_device", "dc_f32_fallbacks",
     "dc_quantise_host_ex", "dc_curvature_to_image_noalloc",
+    "dc_gaussian_blur_host", "dc_gaussian_blur_device", "dc_bilateral_host", "dc_bilateral_device",
 ]
 DC_NOALLOC_MAX_PIXELS = 1 << 24
 DC_PX_U16, DC_PX_U8, DC_PX_I8, DC_PX_I16 = range(4)
@@ -97,6 +98,14 @@ def lib():
         L.dc_median_host.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.dc_median_device.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int,
                                        C.c_void_p, C.c_void_p]
+        L.dc_gaussian_blur_host.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                            C.c_double, C.c_double, C.c_void_p]
+        L.dc_gaussian_blur_device.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                              C.c_double, C.c_double, C.c_void_p, C.c_void_p]
+        L.dc_bilateral_host.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int,
+                                        C.c_double, C.c_double, C.c_void_p]
+        L.dc_bilateral_device.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int,
+                                          C.c_double, C.c_double, C.c_void_p, C.c_void_p]
         L.dc_kernel_launches.restype = C.c_uint64
         L.dc_kernel_launches.argtypes = [C.c_void_p]
         L.dc_last_kernel.restype = C.c_char_p
@@ -245,6 +254,27 @@ class Context:
         out = np.empty_like(frames)
         self._check(self._L.dc_median_host(self._h, kind, frames.ctypes.data, n, ksize,
                                            out.ctypes.data))
+        return out
+
+    @staticmethod
+    def _filter_args(frames):
+        frames = np.ascontiguousarray(frames)
+        kind = {np.dtype(np.uint16): DC_IN_U16_RANGE, np.dtype(np.float32): DC_IN_F32_RANGE}[frames.dtype]
+        return frames, kind, (1 if frames.ndim == 2 else frames.shape[0]), np.empty_like(frames)
+
+    def gaussian_blur(self, frames, ksize, sigma_x, sigma_y=0.0):
+        """preprocess::gaussian_blur on (n, h, w) or (h, w) uint16 / float32 frames;
+        ksize = (width, height)."""
+        frames, kind, n, out = self._filter_args(frames)
+        self._check(self._L.dc_gaussian_blur_host(self._h, kind, frames.ctypes.data, n, ksize[0], ksize[1],
+                                                  sigma_x, sigma_y, out.ctypes.data))
+        return out
+
+    def bilateral(self, frames, d, sigma_color, sigma_space):
+        """preprocess::bilateral_filter on (n, h, w) or (h, w) uint16 / float32 frames."""
+        frames, kind, n, out = self._filter_args(frames)
+        self._check(self._L.dc_bilateral_host(self._h, kind, frames.ctypes.data, n, d, sigma_color,
+                                              sigma_space, out.ctypes.data))
         return out
 
     def quantise(self, quant, feature, mask=None, clamp=(-20.0, 20.0)):

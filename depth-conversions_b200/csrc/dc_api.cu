@@ -2,6 +2,7 @@
 // dispatch and the host-buffer pipeline. See include/depthconv_b200.h.
 #include "../../include/depthconv_b200.h"
 #include "dc_launch.h"
+#include "dc_filters.cuh"
 #include "dc_median.cuh"
 #include "dc_misc_kernels.cuh"
 #include "dc_f64.h"
@@ -12,6 +13,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <map>
 #include <string>
 #include <vector>
@@ -70,6 +72,8 @@ struct dc_ctx {
     // filtered copy of the input frames (dc_job::median_ksize), one per stream:
     // the chunks of dc_convert_host run concurrently on the slots' streams
     std::map<cudaStream_t, dev_buf> d_median;
+    // per-frame scratch of the bilateral filter (min / max, table), one per stream
+    std::map<cudaStream_t, dev_buf> d_bilateral;
     // f32 range input on the guard-free kernels (dc_kernels.cuh kparams::guard):
     // a ring of flags, one per launch in flight, and the count of batches the IEEE
     // kernel had to redo (dc_f32_fallbacks)
@@ -547,6 +551,9 @@ void dc_destroy(dc_ctx* c) {
     cudaDeviceSynchronize();
     drop_device_tables(c);
     dc64::destroy(c->f64);
+    for (auto& kv : c->d_bilateral)
+        if (kv.second.p != nullptr)
+            cudaFree(kv.second.p);
     for (auto& kv : c->d_median)
         free_dev(kv.second);
     if (c->d_guard != nullptr)
@@ -933,6 +940,166 @@ int dc_median_host(dc_ctx* c, int elem_kind, const void* in, int n_frames, int k
         DC_CUDA(c, cudaStreamSynchronize(s.stream));
     }
     return DC_OK;
+}
+
+// ---- preprocess::gaussian_blur / preprocess::bilateral_filter (dc_filters.cuh) ----
+static int filter_check(dc_ctx* c, const char* what, int elem_kind, const void* in, int n_frames,
+                        const void* out) {
+    if (c == nullptr)
+        return DC_ERR_INVALID;
+    if (c->sticky)
+        return DC_ERR_CUDA;
+    if (elem_kind != DC_IN_U16_RANGE && elem_kind != DC_IN_F32_RANGE)
+        return fail(c, DC_ERR_INVALID, std::string(what) + ": elem_kind is DC_IN_U16_RANGE or DC_IN_F32_RANGE");
+    if (n_frames < 0 || (n_frames > 0 && (in == nullptr || out == nullptr)) || in == out)
+        return fail(c, DC_ERR_INVALID, std::string(what) + ": bad buffers");
+    if (c->tabs.cam.w <= 0 || c->tabs.cam.h <= 0)
+        return fail(c, DC_ERR_NO_CAMERA, "frame size unknown: dc_set_frame_size");
+    return DC_OK;
+}
+
+// cv::GaussianBlur's kernel sizes: a size <= 0 is derived from sigma (float / 16 bit
+// images: round(sigma * 8 + 1) | 1), then both must be positive and odd.
+static int gaussian_setup(dc_ctx* c, int kw, int kh, double sx, double sy, dc::flt::gauss_params& p) {
+    if (sy <= 0)
+        sy = sx;
+    if (kw <= 0 && sx > 0)
+        kw = int(std::nearbyint(sx * 4 * 2 + 1)) | 1;
+    if (kh <= 0 && sy > 0)
+        kh = int(std::nearbyint(sy * 4 * 2 + 1)) | 1;
+    if (kw <= 0 || kh <= 0 || kw % 2 != 1 || kh % 2 != 1)
+        return fail(c, DC_ERR_INVALID, "gaussian_blur: kernel sizes must be positive and odd (or 0 with sigma > 0)");
+    if (kw / 2 > dc::flt::kMaxRadius || kh / 2 > dc::flt::kMaxRadius)
+        return fail(c, DC_ERR_UNSUPPORTED, "gaussian_blur: kernel sizes up to 31");
+    p.w  = c->tabs.cam.w;
+    p.h  = c->tabs.cam.h;
+    p.rx = kw / 2;
+    p.ry = kh / 2;
+    dc::flt::gaussian_kernel_host(kw, sx, p.kx);
+    dc::flt::gaussian_kernel_host(kh, sy, p.ky);
+    return DC_OK;
+}
+
+int dc_gaussian_blur_device(dc_ctx* c, int elem_kind, const void* in, int n_frames, int ksize_w,
+                            int ksize_h, double sigma_x, double sigma_y, void* out,
+                            void* cuda_stream) {
+    int rc = filter_check(c, "gaussian_blur", elem_kind, in, n_frames, out);
+    if (rc != DC_OK)
+        return rc;
+    dc::flt::gauss_params p{};
+    rc = gaussian_setup(c, ksize_w, ksize_h, sigma_x, sigma_y, p);
+    if (rc != DC_OK || n_frames == 0)
+        return rc;
+    DC_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = cuda_stream != nullptr ? static_cast<cudaStream_t>(cuda_stream) : c->stream;
+    const cudaError_t e =
+        elem_kind == DC_IN_U16_RANGE
+            ? dc::flt::launch_gaussian(static_cast<const unsigned short*>(in),
+                                       static_cast<unsigned short*>(out), n_frames, p, s)
+            : dc::flt::launch_gaussian(static_cast<const float*>(in), static_cast<float*>(out),
+                                       n_frames, p, s);
+    if (e != cudaSuccess)
+        return cuda_fail(c, e, "gaussian blur kernel launch");
+    c->launches += uint64_t((n_frames + 65534) / 65535);
+    c->last_kernel = "dc::flt::gaussian_blur_kernel";
+    return DC_OK;
+}
+
+// radius = d <= 0 ? round(1.5 sigma_space) : d / 2, at least 1 (bilateralFilter_32f)
+static int bilateral_radius(int d, double sigma_space) {
+    const int r = d <= 0 ? int(std::nearbyint(sigma_space * 1.5)) : d / 2;
+    return std::max(r, 1);
+}
+
+int dc_bilateral_device(dc_ctx* c, int elem_kind, const void* in, int n_frames, int d,
+                        double sigma_color, double sigma_space, void* out, void* cuda_stream) {
+    const int rc = filter_check(c, "bilateral_filter", elem_kind, in, n_frames, out);
+    if (rc != DC_OK)
+        return rc;
+    if (!(sigma_color == sigma_color) || !(sigma_space == sigma_space))
+        return fail(c, DC_ERR_INVALID, "bilateral_filter: sigma is NaN");
+    if (sigma_color <= 0)
+        sigma_color = 1;
+    if (sigma_space <= 0)
+        sigma_space = 1;
+    const int radius = bilateral_radius(d, sigma_space);
+    if (radius > dc::flt::kMaxRadius)
+        return fail(c, DC_ERR_UNSUPPORTED, "bilateral_filter: radius up to 15 (d <= 31)");
+    if (n_frames == 0)
+        return DC_OK;
+    DC_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = cuda_stream != nullptr ? static_cast<cudaStream_t>(cuda_stream) : c->stream;
+    const size_t bytes = size_t(n_frames) * dc::flt::kBilatScratchWords * sizeof(unsigned);
+    dev_buf&     tmp   = c->d_bilateral[s];
+    if (tmp.cap < bytes) {
+        // (a growing buffer is freed only after everything that reads it ran)
+        DC_CUDA(c, cudaStreamSynchronize(s));
+        DC_CUDA(c, reserve_dev(tmp, bytes));
+    }
+    const int         w = c->tabs.cam.w, h = c->tabs.cam.h;
+    unsigned* const   sc = static_cast<unsigned*>(tmp.p);
+    const cudaError_t e =
+        elem_kind == DC_IN_U16_RANGE
+            ? dc::flt::launch_bilateral(static_cast<const unsigned short*>(in),
+                                        static_cast<unsigned short*>(out), w, h, n_frames, radius,
+                                        sigma_color, sigma_space, sc, s)
+            : dc::flt::launch_bilateral(static_cast<const float*>(in), static_cast<float*>(out), w, h,
+                                        n_frames, radius, sigma_color, sigma_space, sc, s);
+    if (e != cudaSuccess)
+        return cuda_fail(c, e, "bilateral filter kernel launch");
+    c->launches += 4 * uint64_t((n_frames + 65534) / 65535);
+    c->last_kernel = "dc::flt::bilateral_kernel";
+    return DC_OK;
+}
+
+// HOST buffers: chunks of frames through staging slot 0, synchronous.
+static int filter_host(dc_ctx* c, int elem_kind, const void* in, int n_frames, void* out,
+                       const std::function<int(const void*, int, void*, cudaStream_t)>& launch) {
+    DC_CUDA(c, cudaSetDevice(c->device));
+    const size_t fb = size_t(c->tabs.cam.w) * c->tabs.cam.h * (elem_kind == DC_IN_U16_RANGE ? 2 : 4);
+    const int chunk = int(std::max<size_t>(1, std::min<size_t>(size_t(n_frames), kChunkTargetBytes / (2 * fb))));
+    slot&     s     = c->slots[0];
+    for (int f0 = 0; f0 < n_frames; f0 += chunk) {
+        const int nf = std::min(chunk, n_frames - f0);
+        int       rc = finish_slot(c, s);
+        if (rc != DC_OK)
+            return rc;
+        DC_CUDA(c, reserve_dev(s.d_in, size_t(chunk) * fb));
+        DC_CUDA(c, reserve_dev(s.d_out[0], size_t(chunk) * fb));
+        DC_CUDA(c, cudaMemcpyAsync(s.d_in.p, static_cast<const char*>(in) + size_t(f0) * fb,
+                                   size_t(nf) * fb, cudaMemcpyHostToDevice, s.stream));
+        rc = launch(s.d_in.p, nf, s.d_out[0].p, s.stream);
+        if (rc != DC_OK)
+            return rc;
+        DC_CUDA(c, cudaMemcpyAsync(static_cast<char*>(out) + size_t(f0) * fb, s.d_out[0].p,
+                                   size_t(nf) * fb, cudaMemcpyDeviceToHost, s.stream));
+        DC_CUDA(c, cudaStreamSynchronize(s.stream));
+    }
+    return DC_OK;
+}
+
+int dc_gaussian_blur_host(dc_ctx* c, int elem_kind, const void* in, int n_frames, int ksize_w,
+                          int ksize_h, double sigma_x, double sigma_y, void* out) {
+    int rc = filter_check(c, "gaussian_blur", elem_kind, in, n_frames, out);
+    if (rc != DC_OK)
+        return rc;
+    dc::flt::gauss_params p{};
+    rc = gaussian_setup(c, ksize_w, ksize_h, sigma_x, sigma_y, p);
+    if (rc != DC_OK || n_frames == 0)
+        return rc;
+    return filter_host(c, elem_kind, in, n_frames, out, [&](const void* di, int nf, void* dout, cudaStream_t st) {
+        return dc_gaussian_blur_device(c, elem_kind, di, nf, ksize_w, ksize_h, sigma_x, sigma_y, dout, st);
+    });
+}
+
+int dc_bilateral_host(dc_ctx* c, int elem_kind, const void* in, int n_frames, int d,
+                      double sigma_color, double sigma_space, void* out) {
+    const int rc = filter_check(c, "bilateral_filter", elem_kind, in, n_frames, out);
+    if (rc != DC_OK || n_frames == 0)
+        return rc;
+    return filter_host(c, elem_kind, in, n_frames, out, [&](const void* di, int nf, void* dout, cudaStream_t st) {
+        return dc_bilateral_device(c, elem_kind, di, nf, d, sigma_color, sigma_space, dout, st);
+    });
 }
 
 int dc_synchronize(dc_ctx* c) {

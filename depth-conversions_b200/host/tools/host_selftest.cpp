@@ -221,7 +221,12 @@ int main(int argc, char** argv) try {
              save_u16(dir + "max_curve.png", convert_max_curve<ushort>(mc)) &&
              save_u16(dir + "scaled.png", depth_scaling(depth, 8., 3.)) &&
              save_u16(dir + "median5.png", preprocess::median_blur(depth, 5)) &&
-             save_f32(dir + "median3.f32", preprocess::median_blur(range, 3));
+             save_f32(dir + "median3.f32", preprocess::median_blur(range, 3)) &&
+             save_f32(dir + "gaussblur.f32", preprocess::gaussian_blur(range, {5, 5}, 1.5)) &&
+             save_u16(dir + "gaussblur.png", preprocess::gaussian_blur(depth, {3, 3}, 0.)) &&
+             save_f32(dir + "bilateral_d.f32", preprocess::bilateral_filter(range, 30., 5)) &&
+             save_f32(dir + "bilateral_s.f32", preprocess::bilateral_filter(range, 30., 2.0)) &&
+             save_u16(dir + "bilateral.png", preprocess::bilateral_filter(depth, 30., 2.0));
         // preconditions: a size mismatch is rejected, not computed
         bool threw = false;
         try {

@@ -263,6 +263,33 @@ int dc_median_host(dc_ctx* ctx, int elem_kind, const void* in, int n_frames, int
 int dc_median_device(dc_ctx* ctx, int elem_kind, const void* in, int n_frames, int ksize,
                      void* out, void* cuda_stream);
 
+/* preprocess::gaussian_blur<PixelType>(image, ksize, sigmaX, sigmaY) = cv::GaussianBlur
+ *   include/sens_loc/preprocess/filter.h:125-136
+ * on n_frames frames of the installed frame size, BORDER_REFLECT_101. ksize_w / ksize_h:
+ * positive and odd (up to 31), or <= 0 to derive the size from sigma as OpenCV does;
+ * sigma_y <= 0 means sigma_x; sigma <= 0 means the kernel OpenCV derives from the size.
+ * elem_kind DC_IN_U16_RANGE or DC_IN_F32_RANGE as for the median; `out` has the type of
+ * `in` and must not alias it. The arithmetic is OpenCV's (not vendored by the reference):
+ * float results agree with cv2 to 1e-6 relative, u16 results to +-1. */
+int dc_gaussian_blur_host(dc_ctx* ctx, int elem_kind, const void* in, int n_frames, int ksize_w,
+                          int ksize_h, double sigma_x, double sigma_y, void* out);
+int dc_gaussian_blur_device(dc_ctx* ctx, int elem_kind, const void* in, int n_frames, int ksize_w,
+                            int ksize_h, double sigma_x, double sigma_y, void* out,
+                            void* cuda_stream);
+
+/* preprocess::bilateral_filter<PixelType>(image, sigma_color, proximity) = cv::bilateralFilter
+ * on the image converted to float
+ *   include/sens_loc/preprocess/filter.h:49-82, apps/depth_filter/filter_functor.h:24-50
+ * `proximity` as the reference's variant: d > 0 is the pixel diameter (sigma_space then
+ * only shapes the spatial weights), d <= 0 derives the radius from sigma_space. sigma <= 0
+ * means 1 (OpenCV 4.3.0). Radius up to 15. u16 frames are converted to float, filtered and
+ * converted back with saturate_cast (math::convert, math/image.h:117-128). The input must
+ * hold no NaN. Agrees with cv2 to 2e-5 of the frame's value range. */
+int dc_bilateral_host(dc_ctx* ctx, int elem_kind, const void* in, int n_frames, int d,
+                      double sigma_color, double sigma_space, void* out);
+int dc_bilateral_device(dc_ctx* ctx, int elem_kind, const void* in, int n_frames, int d,
+                        double sigma_color, double sigma_space, void* out, void* cuda_stream);
+
 /* Block until all work this context enqueued on its own streams has finished. */
 int dc_synchronize(dc_ctx* ctx);
 

@@ -198,6 +198,19 @@ def test_cpp_library_api(tmp_path, oracle):
     assert np.array_equal(cv2.imread(str(tmp_path / "median5.png"), cv2.IMREAD_UNCHANGED),
                           cv2.medianBlur(depth, 5))
     assert np.array_equal(f32("median3"), cv2.medianBlur(f32("range"), 3))
+    # preprocess::gaussian_blur / bilateral_filter (preprocess/filter.h:49-82, 125-136)
+    r32 = f32("range")
+    span = float(r32.max() - r32.min())
+    want = cv2.GaussianBlur(r32, (5, 5), 1.5)
+    assert np.all(np.abs(f32("gaussblur") - want) <= 1e-6 * np.maximum(np.abs(want), 1.0))
+    got = cv2.imread(str(tmp_path / "gaussblur.png"), cv2.IMREAD_UNCHANGED).astype(np.int32)
+    assert np.abs(got - cv2.GaussianBlur(depth, (3, 3), 0).astype(np.int32)).max() <= 1
+    # an int proximity is the diameter, sigma_space 0 -> 1 (OpenCV 4.3.0); a double is sigma_space
+    assert np.abs(f32("bilateral_d") - cv2.bilateralFilter(r32, 5, 30.0, 1.0)).max() <= 2e-5 * span
+    assert np.abs(f32("bilateral_s") - cv2.bilateralFilter(r32, 0, 30.0, 2.0)).max() <= 2e-5 * span
+    got = cv2.imread(str(tmp_path / "bilateral.png"), cv2.IMREAD_UNCHANGED).astype(np.int32)
+    want = np.clip(np.rint(cv2.bilateralFilter(depth.astype(np.float32), 0, 30.0, 2.0)), 0, 65535)
+    assert np.abs(got - want).max() <= 1
 
 
 def test_devices_sharding_in_one_process(scene, oracle, pkg):
