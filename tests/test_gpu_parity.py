@@ -212,13 +212,13 @@ def test_full_size_frames_against_oracle(pkg, gpu_ctx, oracle, w, h):
     frames = np.stack([oracle.synth_depth(0xD2C00003, f, w, h) for f in range(2)])
     f32 = gpu_all_features(pkg, gpu_ctx, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_F32)
     u16 = gpu_all_features(pkg, gpu_ctx, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)
-    i = 1
-    rng = oracle.laserscan(frames[i], k)
-    for f, name in FEATURE_NAMES.items():
-        want = oracle.feature(f, rng, k)
-        assert_float_parity(name, f32[name][i], want)
-        assert_u16_parity(name, u16[name][i], oracle.quantise(f, want, rng))
-    assert_u16_parity("range", u16["range_fused"][i], oracle.quantise(0, rng, rng))
+    for i in range(2):  # both halves of the frame pair
+        rng = oracle.laserscan(frames[i], k)
+        for f, name in FEATURE_NAMES.items():
+            want = oracle.feature(f, rng, k)
+            assert_float_parity(name, f32[name][i], want)
+            assert_u16_parity(name, u16[name][i], oracle.quantise(f, want, rng))
+        assert_u16_parity("range", u16["range_fused"][i], oracle.quantise(0, rng, rng))
 
 
 def test_large_batch_properties(pkg, gpu_ctx, oracle):
@@ -234,13 +234,16 @@ def test_large_batch_properties(pkg, gpu_ctx, oracle):
     for o in outs + [fl]:
         o = o.reshape(n // 4, 4, h, w)
         assert (o == o[0]).all()  # identical frames give identical images wherever they sit
-    rng = oracle.laserscan(base[2], k)
-    for d in range(4):
-        want = oracle.quantise(F_BEARING_H + d, oracle.feature(F_BEARING_H + d, rng, k), rng)
-        assert_u16_parity("bearing", outs[d][254], want)
-        # invalid-depth mask (depth_to_bearing.h:204-207): zero depth -> exactly 0
-        assert not outs[d][254][base[2] == 0].any()
-    assert_u16_parity("flexion", fl[254], oracle.cli_frame(F_FLEXION, 0, base[2], k)[2])
+    # every distinct frame against the oracle, each at another place of the batch (with the
+    # identity above that covers all 256 frames): both halves of a pair, first / last pair
+    for b, at in ((0, 0), (1, 129), (2, 254), (3, 255), (0, 128), (1, 1), (2, 2), (3, 131)):
+        rng = oracle.laserscan(base[b], k)
+        for d in range(4):
+            want = oracle.quantise(F_BEARING_H + d, oracle.feature(F_BEARING_H + d, rng, k), rng)
+            assert_u16_parity("bearing", outs[d][at], want)
+            # invalid-depth mask (depth_to_bearing.h:204-207): zero depth -> exactly 0
+            assert not outs[d][at][base[b] == 0].any()
+        assert_u16_parity("flexion", fl[at], oracle.cli_frame(F_FLEXION, 0, base[b], k)[2])
     # border stays 0 (depth_to_flexion.h:156-161)
     assert not fl[:, 0].any() and not fl[:, -1].any() and not fl[:, :, 0].any() and not fl[:, :, -1].any()
 
