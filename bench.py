@@ -73,6 +73,13 @@ WORKLOADS = {
     "flexion_f32_960x540": dict(w=960, h=540, feature="flexion", out="f32", outs=1, frames=256,
                                 inp="f32", ref_features=[5], config=1,
                                 desc="depth_to_flexion over math::image<float>, 960x540, f32 range -> f32"),
+    # Real = double (what src/unittest/conversion/*.cpp instantiate)
+    "bearing4_f64_960x540": dict(w=960, h=540, feature="bearing", out="f64", outs=4, frames=64,
+                                 ref_features=[1, 2, 3, 4], config=2,
+                                 desc="depth_to_bearing<double> x4, 960x540 pinhole depth, u16 -> 4x f64"),
+    "flexion_f64_960x540": dict(w=960, h=540, feature="flexion", out="f64", outs=1, frames=64,
+                                ref_features=[5], config=1,
+                                desc="depth_to_flexion<double>, 960x540 pinhole depth, u16 -> f64"),
     "range_960x540": dict(w=960, h=540, feature="range", out="u16", outs=1, frames=256,
                           ref_features=[0], config=0,
                           desc="depth2x range, 960x540 pinhole depth, u16 -> u16"),
@@ -247,11 +254,14 @@ def run_reference(args, wl):
     print(json.dumps(line), flush=True)
 
 
+OUT_BYTES = {"u16": 2, "f32": 4, "f64": 8}
+
+
 def algorithmic_bytes(wl, F):
     """Each input pixel read once + each output pixel written once."""
     px = wl["w"] * wl["h"]
     in_b = 4 if wl.get("inp") == "f32" else 2
-    out_b = 2 if wl["out"] == "u16" else 4
+    out_b = OUT_BYTES[wl["out"]]
     total = F * px * (in_b + wl["outs"] * out_b)
     for _, n in wl.get("more", []):
         total += F * px * (in_b + n * out_b)
@@ -282,8 +292,8 @@ class Workload:
         k = kinect_scaled(w, h)
         fmap = {"bearing": pkg.DC_BEARING, "flexion": pkg.DC_FLEXION, "curvature": pkg.DC_CURVATURE,
                 "max_curve": pkg.DC_MAX_CURVE, "range": pkg.DC_RANGE}
-        self.out_kind = pkg.DC_OUT_U16 if wl["out"] == "u16" else pkg.DC_OUT_F32
-        self.out_dtype = torch.uint16 if wl["out"] == "u16" else torch.float32
+        self.out_kind = {"u16": pkg.DC_OUT_U16, "f32": pkg.DC_OUT_F32, "f64": pkg.DC_OUT_F64}[wl["out"]]
+        self.out_dtype = {"u16": torch.uint16, "f32": torch.float32, "f64": torch.float64}[wl["out"]]
         self.extra = wl.get("more", [])
         self.passes = 1 + len(self.extra)
         self.features = [wl["feature"]] + [f for f, _ in self.extra]
@@ -448,7 +458,7 @@ def run_ours(args, wl):
 
     # --- e2e: host buffers through dc_convert_host, the frames and steps of the main leg
     Fe = min(args.e2e_frames or F, F)
-    out_b = 2 if wl["out"] == "u16" else 4
+    out_b = OUT_BYTES[wl["out"]]
     in_b = 4 if wl.get("inp") == "f32" else 2
     h_in = torch.empty((Fe, h, w), dtype=W.d_in.dtype).pin_memory()
     h_in.copy_(W.d_in[:Fe].cpu())
@@ -488,7 +498,7 @@ def run_ours(args, wl):
         "metric": "MPix/s per conversion", "value": value, "unit": "MPix/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "vs_baseline": None, "dtype": "f64" if wl["out"] == "f64" else "f32", "data": "synthetic",
         "config": config_dict(args, wl, F),
         "e2e": {"value": e_value, "unit": "MPix/s", "h2d_bytes_per_step": Fe * px * in_b * W.passes,
                 "d2h_bytes_per_step": Fe * px * n_out_all * out_b,
@@ -522,7 +532,8 @@ def run_ours(args, wl):
         configs = {}
         names = [n for n in ("flexion_960x540", "bearing4_960x540", "curvature_1920x1080",
                              "range_maxcurve_4096x2160", "all_1920x1080", "bearing4_f32_960x540",
-                             "flexion_f32_960x540") if n != args.workload]
+                             "flexion_f32_960x540", "bearing4_f64_960x540", "flexion_f64_960x540")
+                 if n != args.workload]
         for name in names:
             wl2 = WORKLOADS[name]
             X = Workload(pkg, torch, dev, local, stream, wl2, wl2["frames"], 0, 1, sharding)

@@ -65,7 +65,7 @@ struct dc_ctx {
     dev_table    d_range_factor, d_ray[3], d_cos[4], d_curv[3];
     slot         slots[kSlots];
     uint64_t     launches = 0;
-    const char*  last_kernel = "";  // kernel family of the most recent float-path launch
+    const char*  last_kernel = "";  // kernel family of the most recent launch
     // Real = double (dc_f64.h): camera parameters in double, tables on demand
     dc64::camera cam64;
     dc64::state* f64 = nullptr;
@@ -333,6 +333,7 @@ int launch_job(dc_ctx* c, const dc_job* j, cudaStream_t s) {
                                             s, msg, c->launches);
         if (e != cudaSuccess)
             return cuda_fail(c, e, msg.c_str());
+        c->last_kernel = "dc64 (Real = double, one thread per pixel)";
         return DC_OK;
     }
     int in_kind = j->in_kind;

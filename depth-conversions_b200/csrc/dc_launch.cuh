@@ -140,8 +140,8 @@ cudaError_t launch_pair(const kparams& p, int n_frames, cudaStream_t s, launch_i
 }
 
 // Flexion: two columns per thread, so every even width runs it unchanged.
-template <int IN, int OUT>
-cudaError_t launch_flexion_pair(const kparams& p, int n_frames, cudaStream_t s, launch_info& li) {
+template <int IN, int OUT, bool LSB>
+cudaError_t launch_flexion_pair_as(const kparams& p, int n_frames, cudaStream_t s, launch_info& li) {
     // a longer march amortises the point window (three rows of camera-frame points
     // per strip start): 72 rows measured 1.5 % faster than 36 (DC_FLEX_ROWS, read once)
     static const int flex_rows = [] {
@@ -156,16 +156,31 @@ cudaError_t launch_flexion_pair(const kparams& p, int n_frames, cudaStream_t s, 
     if (blocks > 0x7fffffffLL)
         return cudaErrorInvalidConfiguration;
     // per device (one context per GPU in a depth2x --devices N process): not cached
-    const cudaError_t carve = cudaFuncSetAttribute(pr::flexion_pair_kernel<IN, OUT>,
+    const cudaError_t carve = cudaFuncSetAttribute(pr::flexion_pair_kernel<IN, OUT, LSB>,
                                                    cudaFuncAttributePreferredSharedMemoryCarveout,
                                                    int(cudaSharedmemCarveoutMaxShared));
     if (carve != cudaSuccess)
         return carve;
     const size_t smem = size_t(3) * pr::kFlexSlots * pr::kPairThreads * sizeof(uint4);
-    li.kernel   = "dc::pr::flexion_pair_kernel";
+    li.kernel   = LSB ? "dc::pr::flexion_pair_kernel<LSB>" : "dc::pr::flexion_pair_kernel";
     li.launches += 1;
-    pr::flexion_pair_kernel<IN, OUT><<<unsigned(blocks), pr::kPairThreads, smem, s>>>(p, n_frames, rps);
+    pr::flexion_pair_kernel<IN, OUT, LSB><<<unsigned(blocks), pr::kPairThreads, smem, s>>>(p, n_frames, rps);
     return cudaGetLastError();
+}
+
+// 16-bit output: the kernel that is within +-1 LSB of the reference instead of bit exact
+// (dc_pair_kernels.cuh "flexion for 16-bit output"), unless DC_EXACT_U16=1.
+inline bool exact_u16() {
+    static const bool v = env_int("DC_EXACT_U16", 0) != 0;
+    return v;
+}
+template <int IN, int OUT>
+cudaError_t launch_flexion_pair(const kparams& p, int n_frames, cudaStream_t s, launch_info& li) {
+    if constexpr (OUT == OUT_U16) {
+        if (!exact_u16())
+            return launch_flexion_pair_as<IN, OUT, true>(p, n_frames, s, li);
+    }
+    return launch_flexion_pair_as<IN, OUT, false>(p, n_frames, s, li);
 }
 
 // DC_RANGE / DC_SCALE with u16 input: the streaming kernel (8 pixels per thread,

@@ -247,7 +247,19 @@ struct bres {
     f2 q;   // the ratio: its sign selects the reflection
     f2 bc;  // b * c
 };
-template <bool WITH_ACOS = true>
+// 16-bit output (LSB_DIV): the quotient is taken with the raw MUFU.RSQ seed of the radicand
+// as the reciprocal of its (still correctly rounded) square root, without the Newton step
+// that makes the division provably correctly rounded. The residual step squares the seed's
+// 2^-22 error: the quotient is the correctly rounded one except where nom / d lies within
+// 2e-6 ulp of a rounding boundary (about one division in 10^5..10^6), there it is the
+// neighbouring float. One ulp of a ratio at the clamp |q| = 1 - 10 eps, where acos is
+// steepest, moves the angle by 3.9e-5 rad = 0.8 LSB of convert_bearing<ushort> (pi / 65535)
+// and 0.4 LSB of convert_max_curve: inside the +-1 LSB contract of the quantised images.
+// Float output keeps the refined reciprocal (bit-exact ratio).
+#ifndef DC_U16_SKIP_REFINE
+#define DC_U16_SKIP_REFINE 1
+#endif
+template <bool WITH_ACOS = true, bool LSB_DIV = false>
 __device__ __forceinline__ bres bearing_core2(f2 b, f2 c, f2 bb, f2 cc, float cos_alpha) {
     bres     o;
     const f2 ca  = B(cos_alpha);
@@ -264,7 +276,7 @@ __device__ __forceinline__ bres bearing_core2(f2 b, f2 c, f2 bb, f2 cc, float co
 #else
     f2       y;
     const f2 d = sqrt2(rad, y);
-    o.q        = div2(nom, d, rcp_refine2(d, y));
+    o.q        = div2(nom, d, (LSB_DIV && DC_U16_SKIP_REFINE) ? y : rcp_refine2(d, y));
 #endif
     if constexpr (WITH_ACOS)
         o.r = acos_abs2(o.q);

@@ -205,7 +205,7 @@ __device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BE
                             : !DC_BEARING_CARRY_SQ ? mul2(c, c)
                             : d == 1 ? up.s[i + 1] : d == 2 ? up.s[i] : dn.s[i];
             constexpr bool WITH_ACOS = OUT == OUT_U16 && !DC_BEARING_FOLD_Q;
-            const bres k  = bearing_core2<WITH_ACOS>(b, c, bb, cc, cs[i]);
+            const bres k  = bearing_core2<WITH_ACOS, OUT == OUT_U16>(b, c, bb, cc, cs[i]);
             // depth_to_bearing.h:204-207: either depth 0 (or the prior pixel
             // outside the image, which reads as 0) -> 0
             const bool va = k.bc.x != 0.0f, vb = k.bc.y != 0.0f;
@@ -281,8 +281,8 @@ __device__ __forceinline__ void max_curve_row(const kparams& p, const wrow<FEAT_
         // angle_formula (:55-82): 0 if any of the three depths is 0, else the
         // sum of the two bearing angles
         auto pair = [&](f2 dm, f2 smm, f2 dp, f2 spp, float c1, float c2) {
-            const bres k1 = bearing_core2<false>(d0, dm, bb, smm, c1);
-            const bres k2 = bearing_core2<false>(d0, dp, bb, spp, c2);
+            const bres k1 = bearing_core2<false, OUT == OUT_U16>(d0, dm, bb, smm, c1);
+            const bres k2 = bearing_core2<false, OUT == OUT_U16>(d0, dp, bb, spp, c2);
             const f2   s  = add2(acos_signed2(k1.q), acos_signed2(k2.q));
             return make_float2((k1.bc.x != 0.0f && k2.bc.x != 0.0f) ? s.x : 0.0f,
                                (k1.bc.y != 0.0f && k2.bc.y != 0.0f) ? s.y : 0.0f);
@@ -677,7 +677,7 @@ struct edge {
     f2 d, y;  // sqrt(rad), refined reciprocal of it
     f2 bc;    // X * Y: zero iff either depth is zero
 };
-template <bool RAD_FADD>
+template <bool RAD_FADD, bool LSB_DIV = false>
 __device__ __forceinline__ edge edge_shared(f2 x, f2 y, f2 xx, f2 yy, float cu) {
     edge     e;
     const f2 sum = add2(xx, yy);
@@ -697,7 +697,7 @@ __device__ __forceinline__ edge edge_shared(f2 x, f2 y, f2 xx, f2 yy, float cu) 
     }
     f2       seed;
     e.d = sqrt2(rad, seed);
-    e.y = rcp_refine2(e.d, seed);
+    e.y = (LSB_DIV && DC_U16_SKIP_REFINE) ? seed : rcp_refine2(e.d, seed);  // (dc_pair.cuh bearing_core2)
     return e;
 }
 #define DC_MC_INVALID (-1.0e30f)
@@ -889,7 +889,7 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
 #pragma unroll
             for (int j = 0; j < 5; ++j) {
                 const float c = cs_(cs.h[j]);
-                const edge  e = edge_shared<!TAB>(mid.r[j], mid.r[j + 1], mid.s[j], mid.s[j + 1], c);
+                const edge  e = edge_shared<!TAB, OUT == OUT_U16>(mid.r[j], mid.r[j + 1], mid.s[j], mid.s[j + 1], c);
                 if (j >= 1)  // pixel j looks right; angle_formula (:55-82): back + forward
                     m[j - 1] = add2(hb, edge_end(mid.r[j], yc(mid, j + 1, c), e));
                 if (j <= 3)  // pixel j+1 looks left
@@ -905,7 +905,7 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
         for (int i = 0; i < 4; ++i) {
             const int   c  = i + 1;
             const float co = cs_(cs.v[i]);
-            const edge  e  = edge_shared<!TAB>(mid.r[c], dn.r[c], mid.s[c], dn.s[c], co);
+            const edge  e  = edge_shared<!TAB, OUT == OUT_U16>(mid.r[c], dn.r[c], mid.s[c], dn.s[c], co);
             if constexpr (STORE)
                 take(i, cget(i), edge_end(mid.r[c], yc(dn, c, co), e));
             cset(i, edge_end(dn.r[c], yc(mid, c, co), e));
@@ -917,7 +917,7 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
 #pragma unroll
             for (int c = 0; c < 5; ++c) {
                 const float co = cs_(cs.d[c]);
-                const edge  e  = edge_shared<!TAB>(mid.r[c], dn.r[c + 1], mid.s[c], dn.s[c + 1], co);
+                const edge  e  = edge_shared<!TAB, OUT == OUT_U16>(mid.r[c], dn.r[c + 1], mid.s[c], dn.s[c + 1], co);
                 if (c >= 1) {
                     if constexpr (STORE)
                         take(c - 1, cget(4 + c - 1), edge_end(mid.r[c], yc(dn, c + 1, co), e));
@@ -934,7 +934,7 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
 #pragma unroll
         for (int c = 1; c < 6; ++c) {
             if constexpr (!TAB) {
-                const edge e = edge_shared<!TAB>(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], cu);
+                const edge e = edge_shared<!TAB, OUT == OUT_U16>(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], cu);
                 if constexpr (STORE)
                     if (c <= 4)
                         take(c - 1, cget(8 + c - 1), edge_end(mid.r[c], dn.c[c - 1], e));
@@ -944,12 +944,12 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
                 if constexpr (STORE)
                     if (c <= 4) {
                         const float co = cs.d[c];  // D(u + 1, v + 1), u = u0 + c - 1
-                        const edge  e  = edge_shared<!TAB>(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], co);
+                        const edge  e  = edge_shared<!TAB, OUT == OUT_U16>(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], co);
                         take(c - 1, cget(8 + c - 1), edge_end(mid.r[c], mul2(dn.r[c - 1], B(co)), e));
                     }
                 if (c >= 2) {
                     const float co = cs.a[c - 2];  // A(u0 + c - 1, v)
-                    const edge  e  = edge_shared<!TAB>(dn.r[c - 1], mid.r[c], dn.s[c - 1], mid.s[c], co);
+                    const edge  e  = edge_shared<!TAB, OUT == OUT_U16>(dn.r[c - 1], mid.r[c], dn.s[c - 1], mid.s[c], co);
                     cset(8 + c - 2, edge_end(dn.r[c - 1], mul2(mid.r[c], B(co)), e));
                 }
             }
@@ -1059,6 +1059,49 @@ __device__ __forceinline__ v3 cross3(const v3& a, const v3& b) {
             sub2(mul2(a.x, b.y), mul2(a.y, b.x))};
 }
 
+// ---- flexion for 16-bit output, within the +-1 LSB contract (BASELINE.json north_star:
+// "8/16-bit quantised output images within +-1 LSB") instead of bit for bit --------------
+// One LSB of convert_flexion<ushort> is 1 / 65535 = 1.5e-5 of a value in [0, 1]. The
+// exact path spends 11 of the 22 packed operations of every normalisation on a correctly
+// rounded sqrt and three correctly rounded divisions; what the 16-bit image needs is the
+// value to 1e-5. Differences of points, dot and cross products keep the reference's
+// operations and order; only the division by the norm changes:
+//   mode 1: n / |n| as n * rsqrt(n.n)            (MUFU.RSQ: 2^-22 relative)
+//   mode 2: the four divisions moved behind the products,
+//             dot(v0 x v1, v2 x v3) * rsqrt(|v0|^2 |v1|^2) * rsqrt(|v2|^2 |v3|^2)
+//           (range values lie in [2^-10, 2^22]: the products stay inside [2e-22, 4e28]).
+// Error against the exact path: each cross-product component carries <= 2e-7 of
+// |a||b|, the dot product of two of them <= 1.5e-6, the two scale factors <= 6e-7:
+// together < 3e-6 = 0.2 LSB, so the rounded images differ by at most 1 (where the exact
+// value sits within 0.2 LSB of a rounding boundary). A null vector (both points at the
+// origin) gives 0 as in the reference: 0 * rsqrt(2^-100) = 0.
+// DC_EXACT_U16=1 in the environment selects the bit-exact kernel for 16-bit output too.
+#ifndef DC_FLEX_LSB_MODE
+#define DC_FLEX_LSB_MODE 1
+#endif
+__device__ __forceinline__ f2 clamp_tiny2(f2 z) {
+    return make_float2(fmaxf(z.x, 7.888609052210118e-31f), fmaxf(z.y, 7.888609052210118e-31f));
+}
+__device__ __forceinline__ v3 normalized3_lsb(const v3& n) {
+    const f2 y = rsq2(clamp_tiny2(dot3(n, n)));
+    return {mul2(n.x, y), mul2(n.y, y), mul2(n.z, y)};
+}
+// |dot(n0 x n1, n2 x n3)| before the clamp to [0, 1], from the four unnormalised vectors
+template <bool LSB>
+__device__ __forceinline__ f2 flexion_value(const v3& v0, const v3& v1, const v3& v2, const v3& v3_) {
+    if constexpr (!LSB) {
+        return dot3(cross3(normalized3(v0), normalized3(v1)), cross3(normalized3(v2), normalized3(v3_)));
+    } else if constexpr (DC_FLEX_LSB_MODE == 1) {
+        return dot3(cross3(normalized3_lsb(v0), normalized3_lsb(v1)),
+                    cross3(normalized3_lsb(v2), normalized3_lsb(v3_)));
+    } else {
+        const f2 s01 = clamp_tiny2(mul2(dot3(v0, v0), dot3(v1, v1)));
+        const f2 s23 = clamp_tiny2(mul2(dot3(v2, v2), dot3(v3_, v3_)));
+        const f2 x   = dot3(cross3(v0, v1), cross3(v2, v3_));
+        return mul2(mul2(x, rsq2(s01)), rsq2(s23));
+    }
+}
+
 constexpr int kFlexSlots = 6;
 // slot 0: [A: 2 px | B: 2 px | A word with u0-1 (high half) | B word with u0-1]
 // slot 1: [A word with u0+2 (low half) | B word | factor(u0-1) | factor(u0+2)]
@@ -1156,10 +1199,122 @@ __device__ __forceinline__ void flex_points(const flane& L, float ufac, const ui
     }
 }
 
+// ---- conflict-free staging layout of the 16-bit kernel (DC_FLEX_STAGE_WORDS=1) ----------
+// The slot layout above puts the 16 bytes of a thread's slot side by side: a 4- or 8-byte
+// cp.async of a warp then lands 16 bytes apart, four lanes per bank (ncu, round 2: 60.6 M
+// of the 79 M shared-memory wavefronts of the kernel's LDGSTS were bank conflicts, and the
+// L1TEX data stage was the busiest unit of the SM at 62 %; with the 16-bit kernel's shorter
+// arithmetic it became the bound). Here every staged item is its own array over the CTA:
+//   4-byte item j of thread t:  word  [j * T + t]                      (j < kFlexWords)
+//   8-byte item p of thread t:  dword [kFlexWords * T / 2 + p * T + t] (p < kFlexPairs)
+// consecutive lanes hit consecutive banks for writes and read-backs alike. Same footprint
+// (96 bytes per thread and stage); 18 LDS.32 / LDS.64 per row step instead of 6 LDS.128.
+// u16 input: words 0 A(u0,u0+1) 1 B(..) 2 A-left word 3 B-left 4 A-right 5 B-right
+//            6 fac(u0-1) 7 fac(u0+2); pair 0 fac(u0,u0+1)
+// f32 input: words 0 A(u0-1) 1 B(u0-1) 2 A(u0+2) 3 B(u0+2); pairs 0 A(u0,u0+1) 4 B(u0,u0+1)
+// both:      words 8 rx(u0-1) 9 rx(u0+2) 10 ry(u0-1) 11 ry(u0+2) 12 rz(u0-1) 13 rz(u0+2);
+//            pairs 1 rx(u0,u0+1) 2 ry(..) 3 rz(..)
+#ifndef DC_FLEX_STAGE_WORDS
+#define DC_FLEX_STAGE_WORDS 1
+#endif
+constexpr int kFlexWords = 14, kFlexPairs = 5;
+static_assert(kFlexWords * 4 + kFlexPairs * 8 == kFlexSlots * 16, "same footprint as the slot layout");
+struct flex_stage {
+    char* base;  // of the stage, for this thread: word j at base + j * 4 T, pair p at pairs + p * 8 T
+    char* pairs;
+    __device__ __forceinline__ char* word(int j, int T) const { return base + j * 4 * T; }
+    __device__ __forceinline__ char* pair(int p, int T) const { return pairs + p * 8 * T; }
+};
+__device__ __forceinline__ flex_stage flex_stage_of(uint4* smem, int stage, int T, int t) {
+    char* b = reinterpret_cast<char*>(smem) + size_t(stage) * kFlexSlots * 16 * T;
+    return {b + 4 * t, b + kFlexWords * 4 * T + 8 * t};
+}
+
+template <int IN>
+__device__ __forceinline__ void flex_issue(const flane& L, int roff, bool in, const flex_stage& st, int T) {
+    const bool l = in && L.hl, r = in && L.hr;
+    const int  ol = L.hl ? -2 : 0, orr = L.hr ? 2 : 0, ol1 = L.hl ? -1 : 0;
+    if constexpr (IN == IN_F32_RANGE) {
+        const float *a = L.Af + roff, *b = L.Bff + roff;
+        cp_async<8>(st.pair(0, T), a, in);
+        cp_async<8>(st.pair(4, T), b, in);
+        cp_async<4>(st.word(0, T), a + ol1, l);
+        cp_async<4>(st.word(1, T), b + ol1, l);
+        cp_async<4>(st.word(2, T), a + orr, r);
+        cp_async<4>(st.word(3, T), b + orr, r);
+    } else {
+        const unsigned short *a = L.A + roff, *b = L.Bf + roff;
+        cp_async<4>(st.word(0, T), a, in);
+        cp_async<4>(st.word(1, T), b, in);
+        cp_async<4>(st.word(2, T), a + ol, l);
+        cp_async<4>(st.word(3, T), b + ol, l);
+        cp_async<4>(st.word(4, T), a + orr, r);
+        cp_async<4>(st.word(5, T), b + orr, r);
+    }
+    if (IN == IN_U16_DEPTH && L.fac != nullptr) {
+        const float* f = L.fac + roff;
+        cp_async<4>(st.word(6, T), f + ol1, l);
+        cp_async<4>(st.word(7, T), f + orr, r);
+        cp_async<8>(st.pair(0, T), f, in);
+    }
+    const float *x = L.rx + roff, *y = L.ry + roff, *z = L.rz + roff;
+    cp_async<4>(st.word(8, T), x + ol1, l);
+    cp_async<4>(st.word(9, T), x + orr, r);
+    cp_async<4>(st.word(10, T), y + ol1, l);
+    cp_async<4>(st.word(11, T), y + orr, r);
+    cp_async<4>(st.word(12, T), z + ol1, l);
+    cp_async<4>(st.word(13, T), z + orr, r);
+    cp_async<8>(st.pair(1, T), x, in);
+    cp_async<8>(st.pair(2, T), y, in);
+    cp_async<8>(st.pair(3, T), z, in);
+}
+
+template <int IN>
+__device__ __forceinline__ void flex_points(const flane& L, float ufac, const flex_stage& st, int T,
+                                            v3 (&P)[4], f32_window& win) {
+    auto W  = [&](int j) { return *reinterpret_cast<const unsigned*>(st.word(j, T)); };
+    auto Wf = [&](int j) { return *reinterpret_cast<const float*>(st.word(j, T)); };
+    auto Pf = [&](int p) { return *reinterpret_cast<const float2*>(st.pair(p, T)); };
+    f2 d[4];
+    if constexpr (IN == IN_F32_RANGE) {
+        const float2 a = Pf(0), b = Pf(4);
+        d[0] = make_float2(Wf(0), Wf(1));
+        d[1] = make_float2(a.x, b.x);
+        d[2] = make_float2(a.y, b.y);
+        d[3] = make_float2(Wf(2), Wf(3));
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            win.see(d[i].x, d[i].y);
+    } else {
+        const unsigned a = W(0), b = W(1);
+        d[0] = make_float2(magic_hi(W(2)), magic_hi(W(3)));
+        d[1] = make_float2(magic_lo(a), magic_lo(b));
+        d[2] = make_float2(magic_hi(a), magic_hi(b));
+        d[3] = make_float2(magic_lo(W(4)), magic_lo(W(5)));
+    }
+    const bool tab = IN == IN_U16_DEPTH && L.fac != nullptr;
+    float      fc[4] = {ufac, ufac, ufac, ufac};
+    if (tab) {
+        const float2 f = Pf(0);
+        fc[0] = Wf(6), fc[1] = f.x, fc[2] = f.y, fc[3] = Wf(7);
+    }
+    const float2 x = Pf(1), y = Pf(2), z = Pf(3);
+    const float  rx[4] = {Wf(8), x.x, x.y, Wf(9)};
+    const float  ry[4] = {Wf(10), y.x, y.y, Wf(11)};
+    const float  rz[4] = {Wf(12), z.x, z.y, Wf(13)};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        f2 r = IN == IN_F32_RANGE ? d[i] : add2(d[i], B(-8388608.0f));
+        if constexpr (IN == IN_U16_DEPTH)
+            r = mul2(r, B(fc[i]));
+        P[i] = {mul2(r, B(rx[i])), mul2(r, B(ry[i])), mul2(r, B(rz[i]))};
+    }
+}
+
 #ifndef DC_FLEX_BLOCKS
 #define DC_FLEX_BLOCKS 3
 #endif
-template <int IN, int OUT>
+template <int IN, int OUT, bool LSB = false>
 __global__ void __launch_bounds__(kPairThreads, DC_FLEX_BLOCKS)
     flexion_pair_kernel(const __grid_constant__ kparams p, int n_frames, int rows_per_strip) {
     const int       groups_x = p.w >> 1;
@@ -1204,9 +1359,15 @@ __global__ void __launch_bounds__(kPairThreads, DC_FLEX_BLOCKS)
     // for cp.async groups (ncu: long scoreboard at the wait).
     extern __shared__ uint4 smem[];
     constexpr int T    = kPairThreads;
-    uint4* const  stg0 = smem + threadIdx.x;
-    uint4* const  stg1 = smem + kFlexSlots * T + threadIdx.x;
-    uint4* const  stg2 = smem + 2 * kFlexSlots * T + threadIdx.x;
+    // the word layout for the 16-bit kernel (L1TEX bound: 0.537 -> 0.495 ms), the slot layout
+    // for the exact ones (register-read / FMA bound: the twelve extra LDS cost them 1-4 %)
+    auto stage = [&](int g) {
+        if constexpr (LSB && DC_FLEX_STAGE_WORDS)
+            return flex_stage_of(smem, g, T, threadIdx.x);
+        else
+            return smem + g * kFlexSlots * T + threadIdx.x;
+    };
+    const auto stg0 = stage(0), stg1 = stage(1), stg2 = stage(2);
 
     v3 w0[4], w1[4], w2[4];
     flex_issue<IN>(L, max(v0 - 1, 0) * w, v0 >= 1, stg0, T);
@@ -1241,11 +1402,8 @@ __global__ void __launch_bounds__(kPairThreads, DC_FLEX_BLOCKS)
             const int c  = i + 1;                                                              \
             /* :105-127: (u,v-1)->(u,v+1), (u-1,v)->(u+1,v), (u+1,v-1)->(u-1,v+1),        */   \
             /*           (u-1,v-1)->(u+1,v+1)                                              */   \
-            const v3 n0 = normalized3(sub3(DN[c], UP[c]));                                     \
-            const v3 n1 = normalized3(sub3(MID[c + 1], MID[c - 1]));                           \
-            const v3 n2 = normalized3(sub3(DN[c - 1], UP[c + 1]));                             \
-            const v3 n3 = normalized3(sub3(DN[c + 1], UP[c - 1]));                             \
-            const f2 x  = dot3(cross3(n0, n1), cross3(n2, n3));                                \
+            const f2 x  = flexion_value<LSB>(sub3(DN[c], UP[c]), sub3(MID[c + 1], MID[c - 1]),  \
+                                             sub3(DN[c - 1], UP[c + 1]), sub3(DN[c + 1], UP[c - 1])); \
             const bool ok = rin && (i == 0 ? cin0 : cin1);                                     \
             f[i] = make_float2(ok ? fminf(fabsf(x.x), 1.0f) : 0.0f,                            \
                                ok ? fminf(fabsf(x.y), 1.0f) : 0.0f);                           \

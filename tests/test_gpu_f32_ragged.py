@@ -95,7 +95,7 @@ def test_even_ragged_widths_run_the_pair_kernels(pkg, gpu_ctx, oracle, w, h, n):
     gpu_ctx.convert(P.DC_BEARING, frames, P.DC_IN_U16_DEPTH, P.DC_OUT_U16, want=(True,) * 4)
     assert gpu_ctx.last_kernel == "dc::pr::pair_kernel<SPEC_HALF>"
     gpu_ctx.convert(P.DC_FLEXION, frames, P.DC_IN_U16_DEPTH, P.DC_OUT_U16)
-    assert gpu_ctx.last_kernel == "dc::pr::flexion_pair_kernel"
+    assert gpu_ctx.last_kernel == "dc::pr::flexion_pair_kernel<LSB>"
     u16 = gpu_all_features(pkg, gpu_ctx, frames, P.DC_IN_U16_DEPTH, P.DC_OUT_U16, clamp=(-5.0, 11.0))
     lib = gpu_all_features(pkg, gpu_ctx, f32["range"], P.DC_IN_F32_RANGE, P.DC_OUT_F32)
     assert gpu_ctx.last_kernel == "dc::pr::pair_kernel<SPEC_HALF>"

@@ -153,7 +153,7 @@ def test_scale_and_pinhole_range_roundtrip(pkg, gpu_ctx, oracle):
     rng_u16 = gpu_ctx.convert(pkg.DC_RANGE, d, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)[0]
     fl = gpu_ctx.convert(pkg.DC_FLEXION, rng_u16, pkg.DC_IN_U16_RANGE, pkg.DC_OUT_U16)[0]
     _, _, want = oracle.cli_frame(F_FLEXION, 1, rng_u16, k)
-    assert np.array_equal(fl, want)
+    assert_u16_parity("flexion", fl, want)
 
 
 def test_bad_jobs_are_rejected(pkg, gpu_ctx):
@@ -288,7 +288,7 @@ def test_kernel_selection_is_reported(pkg, gpu_ctx, oracle):
     gpu_ctx.convert(pkg.DC_MAX_CURVE, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)
     assert gpu_ctx.last_kernel == "dc::pr::maxcurve_edge_kernel<SPEC_TABLES>"
     gpu_ctx.convert(pkg.DC_FLEXION, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)
-    assert gpu_ctx.last_kernel == "dc::pr::flexion_pair_kernel"
+    assert gpu_ctx.last_kernel == "dc::pr::flexion_pair_kernel<LSB>"
     gpu_ctx.convert(pkg.DC_RANGE, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)
     assert gpu_ctx.last_kernel == "dc::pr::stream_kernel"
     set_k(gpu_ctx, kinect_scaled(322, 203))
@@ -326,3 +326,53 @@ def test_equirectangular_float_against_compiled_reference(pkg, gpu_ctx, oracle, 
             ref.lib.ref_feature_equi_f32(f, rng.ctypes.data, w, h, tmin, tmax, want.ctypes.data)
             assert_float_parity(name, f32[name][i], want)
             assert_float_parity(name, lib[name][i], want)
+
+
+def test_flexion_u16_lsb_kernel_and_exact_switch(pkg, gpu_ctx, oracle, tmp_path):
+    """16-bit flexion (what depth2x writes) comes from the kernel that divides by the norms
+    with MUFU.RSQ: within +-1 LSB of the reference (in fact < 0.2 LSB before rounding, so
+    only pixels at a rounding boundary move). DC_EXACT_U16=1 selects the bit-exact kernel;
+    the float image is bit exact either way."""
+    import subprocess
+    import sys as _sys
+    w, h = 960, 540
+    k = kinect_scaled(w, h)
+    set_k(gpu_ctx, k)
+    frames = np.stack([oracle.synth_depth(0xD2C000C1, f, w, h) for f in range(3)])
+    got = gpu_ctx.convert(pkg.DC_FLEXION, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)[0]
+    assert gpu_ctx.last_kernel == "dc::pr::flexion_pair_kernel<LSB>"
+    f32 = gpu_ctx.convert(pkg.DC_FLEXION, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_F32)[0]
+    assert gpu_ctx.last_kernel == "dc::pr::flexion_pair_kernel"
+    moved = 0
+    for i in range(3):
+        rng = oracle.laserscan(frames[i], k)
+        want32 = oracle.feature(F_FLEXION, rng, k)
+        assert_float_parity("flexion", f32[i], want32)
+        want = oracle.quantise(F_FLEXION, want32, rng)
+        d = np.abs(got[i].astype(np.int32) - want.astype(np.int32))
+        assert d.max() <= 1
+        moved += int((d > 0).sum())
+        # before rounding the two kernels are < 0.2 LSB apart: a pixel can only move if the
+        # exact value lies that close to a rounding boundary (k + 0.5)
+        frac = np.abs((want32.astype(np.float64) * 65535.0) % 1.0 - 0.5)
+        assert (frac[d > 0] < 0.2).all()
+    assert moved < 0.1 * frames.size
+    np.save(tmp_path / "frames.npy", frames)
+    code = (
+        "import sys, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "from conftest import load_pkg; pkg = load_pkg()\n"
+        "fr = np.load(%r)\n"
+        "with pkg.Context(0) as c:\n"
+        "    c.set_pinhole(%d, %d, %r, %r, %r, %r)\n"
+        "    out = c.convert(pkg.DC_FLEXION, fr, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)[0]\n"
+        "    assert c.last_kernel == 'dc::pr::flexion_pair_kernel', c.last_kernel\n"
+        "np.save(%r, out)\n"
+    ) % (os.path.dirname(os.path.abspath(__file__)), os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+         str(tmp_path / "frames.npy"), w, h, k["fx"], k["fy"], k["cx"], k["cy"], str(tmp_path / "exact.npy"))
+    r = subprocess.run([_sys.executable, "-c", code], env=dict(os.environ, DC_EXACT_U16="1"),
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    exact = np.load(tmp_path / "exact.npy")
+    for i in range(3):
+        rng = oracle.laserscan(frames[i], k)
+        assert np.array_equal(exact[i], oracle.quantise(F_FLEXION, oracle.feature(F_FLEXION, rng, k), rng))

@@ -121,7 +121,7 @@ def main():
             if first:
                 worst = {}
                 for _, pat, fid in outs:
-                    exact = fid in (F_RANGE, F_FLEXION)
+                    exact = fid == F_RANGE
                     dmax = 0
                     for i in (0, 3, a.frames - 1):
                         got = cv2.imread(os.path.join(work, pat.format(i)), cv2.IMREAD_UNCHANGED)

@@ -76,7 +76,8 @@ for wl, tr in traffic.items():
     m = re.match(r"void (\w+)<([^>]*)>", kn)
     if not m or m.group(1) == "stream_kernel":
         continue
-    key = m.group(1) + "I" + "".join(f"Li{a.strip()}E" for a in m.group(2).split(",")) + "E"
+    key = m.group(1) + "I" + "".join({"true": "Lb1E", "false": "Lb0E"}.get(a.strip(), f"Li{a.strip()}E")
+                                     for a in m.group(2).split(",")) + "E"
     steps, pixels = next(v for k, v in STEPS.items() if kn[5:].startswith(k))
     b = last_json(f"{G}/{tag}_bench_{wl}.json")
     c = b["config"]
