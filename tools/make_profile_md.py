@@ -76,8 +76,11 @@ for wl, tr in traffic.items():
     m = re.match(r"void (\w+)<([^>]*)>", kn)
     if not m or m.group(1) == "stream_kernel":
         continue
-    key = m.group(1) + "I" + "".join({"true": "Lb1E", "false": "Lb0E"}.get(a.strip(), f"Li{a.strip()}E")
-                                     for a in m.group(2).split(",")) + "E"
+    targs = [a.strip() for a in m.group(2).split(",")]
+    codes = [{"true": "Lb1E", "false": "Lb0E"}.get(a, f"Li{a}E") for a in targs]
+    if m.group(1) == "flexion_pair_kernel" and len(codes) == 3:  # <IN, OUT, bool LSB>: ncu prints the bool as 0 / 1
+        codes[2] = f"Lb{targs[2][-1] if targs[2] in ('0', '1') else int(targs[2] == 'true')}E"
+    key = m.group(1) + "I" + "".join(codes) + "E"
     steps, pixels = next(v for k, v in STEPS.items() if kn[5:].startswith(k))
     b = last_json(f"{G}/{tag}_bench_{wl}.json")
     c = b["config"]
