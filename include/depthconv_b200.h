@@ -103,7 +103,16 @@ typedef enum dc_out_kind {
                        <ushort> (depth_to_flexion.h:194-215), convert_max_curve
                        <ushort> (depth_to_max_curve.h:156-176), curvature_to_image
                        <ushort> with both clamps (depth_to_curvature.h:253-283),
-                       convertTo(CV_16U) for range (converter_laserscan.h.inl:9-10) */
+                       convertTo(CV_16U) for range (converter_laserscan.h.inl:9-10).
+                       Accuracy: within +-1 of the reference's 16 bit image (range
+                       and the curvatures: equal). The fused kernels use that
+                       margin: bearing / max-curve fold scale and rounding into
+                       one operation and take the ratio with an unrefined
+                       reciprocal (<= 0.8 LSB at the acos clamp), flexion divides
+                       by the norms with a 2^-22 reciprocal square root (< 0.2 LSB).
+                       DC_EXACT_U16=1 in the environment selects the bit-exact
+                       flexion kernel; quantising a DC_OUT_F32 image with
+                       dc_quantise_host reproduces the reference's two-step result. */
     DC_OUT_F64 = 2  /* Real = double: every operation of the path in double, as the
                        reference's templates instantiated with double compute it
                        (camera from dc_set_*_f64, or the float parameters widened).

@@ -376,3 +376,47 @@ def test_flexion_u16_lsb_kernel_and_exact_switch(pkg, gpu_ctx, oracle, tmp_path)
     for i in range(3):
         rng = oracle.laserscan(frames[i], k)
         assert np.array_equal(exact[i], oracle.quantise(F_FLEXION, oracle.feature(F_FLEXION, rng, k), rng))
+
+
+@pytest.mark.parametrize("w,h", [(960, 540), (1920, 1080)])
+def test_u16_kernels_at_depth_discontinuities(pkg, gpu_ctx, oracle, w, h):
+    """The 16-bit bearing / max-curve kernels take nom / sqrt(rad) with an unrefined reciprocal
+    (<= 1 ulp off in rare cases): worst where acos is steepest, |ratio| -> 1, i.e. where the
+    chord to the neighbour runs along the ray. Frames made of such chords: depth jumps of up to
+    60 m between neighbouring pixels in every direction, plus smooth parts and holes. 16-bit
+    images within +-1 of the reference's, float images within 1e-5 (per-camera tables at
+    960x540, one scalar angle at 1920x1080)."""
+    k = kinect_scaled(w, h)
+    set_k(gpu_ctx, k)
+    rs = np.random.RandomState(w)
+    base = oracle.synth_depth(0xD2C000D1, 0, w, h).astype(np.int64)
+    frames = []
+    for kind in range(4):
+        f = base.copy()
+        jump = rs.choice([0, 300, 5000, 20000, 60000], size=(h, w), p=[0.5, 0.2, 0.15, 0.1, 0.05])
+        if kind == 1:   # vertical stripes: every horizontal / diagonal chord is a jump
+            jump = np.where((np.arange(w)[None, :] // 1) % 2 == 0, 0, 40000) + 0 * jump
+        elif kind == 2:  # checkerboard
+            jump = np.where((np.arange(w)[None, :] + np.arange(h)[:, None]) % 2 == 0, 0, 55000)
+        elif kind == 3:  # near and far values next to each other, tiny near values
+            f = np.where(rs.rand(h, w) < 0.5, 1 + (f % 7), 65535 - (f % 11))
+            jump = 0 * jump
+        f = np.where(base == 0, 0, np.clip(f + jump, 0, 65535))
+        frames.append(f.astype(np.uint16))
+    frames = np.stack(frames)
+    b16 = gpu_ctx.convert(pkg.DC_BEARING, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16, want=(True,) * 4)
+    b32 = gpu_ctx.convert(pkg.DC_BEARING, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_F32, want=(True,) * 4)
+    m16 = gpu_ctx.convert(pkg.DC_MAX_CURVE, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)[0]
+    fl16 = gpu_ctx.convert(pkg.DC_FLEXION, frames, pkg.DC_IN_U16_DEPTH, pkg.DC_OUT_U16)[0]
+    steep = 0
+    for i in range(frames.shape[0]):
+        rng = oracle.laserscan(frames[i], k)
+        for d in range(4):
+            want = oracle.feature(F_BEARING_H + d, rng, k)
+            assert_float_parity("bearing", b32[d][i], want)
+            assert_u16_parity("bearing", b16[d][i], oracle.quantise(F_BEARING_H + d, want, rng))
+            steep += int(((want > 0) & ((want < 0.01) | (want > np.pi - 0.01))).sum())
+        want = oracle.feature(F_MAX_CURVE, rng, k)
+        assert_u16_parity("max_curve", m16[i], oracle.quantise(F_MAX_CURVE, want, rng))
+        assert_u16_parity("flexion", fl16[i], oracle.cli_frame(F_FLEXION, 0, frames[i], k)[2])
+    assert steep > 10000, steep  # the frames do exercise the steep end of acos
