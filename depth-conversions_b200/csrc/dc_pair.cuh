@@ -136,6 +136,30 @@ __device__ __forceinline__ f2 div2_fast(f2 a, f2 b) { return div2(a, b, rcp_refi
 // The caller reflects for q < 0 (acos(q) = pi - acos(|q|)); together that is
 // acos(clamp(q, -1 + delta, 1 - delta)) of math/triangles.h:55-58. A NaN q
 // (only on lanes that are masked out afterwards) comes out finite.
+// P(a) of acos(a) = sqrt(1 - a) P(a). P5: the float path (relative error < 1.2e-6).
+// P4 (16-bit output only, DC_U16_ACOS_DEG=4): fitted for the ABSOLUTE error of the angle,
+// max 5.0e-6 rad in float evaluation = 0.10 LSB of convert_bearing<ushort> (pi / 65535); near
+// the clamp, where the unrefined quotient may cost 0.8 LSB (bearing_core2), its error is
+// 3.6e-5 of an angle of 1.5e-3 rad: nothing. One FFMA2 less per angle pair.
+#ifndef DC_U16_ACOS_DEG
+#define DC_U16_ACOS_DEG 4
+#endif
+template <bool LSB = false>
+__device__ __forceinline__ f2 acos_poly2(f2 a) {
+    if constexpr (LSB && DC_U16_ACOS_DEG == 4) {
+        f2 p = fma2(B(0.009730911813676357f), a, B(-0.03761417418718338f));
+        p    = fma2(p, a, B(0.08563580363988876f));
+        p    = fma2(p, a, B(-0.21428003907203674f));
+        return fma2(p, a, B(1.570791482925415f));
+    } else {
+        f2 p = fma2(B(-0.004307856317609549f), a, B(0.0192753653973341f));
+        p    = fma2(p, a, B(-0.044893890619277954f));
+        p    = fma2(p, a, B(0.08785323798656464f));
+        p    = fma2(p, a, B(-0.2145095020532608f));
+        return fma2(p, a, B(1.5707951784133911f));
+    }
+}
+template <bool LSB = false>
 __device__ __forceinline__ f2 acos_abs2(f2 q) {
     const f2 a = make_float2(fminf(fabsf(q.x), DC_ONE_MINUS_DELTA),
                              fminf(fabsf(q.y), DC_ONE_MINUS_DELTA));
@@ -150,11 +174,7 @@ __device__ __forceinline__ f2 acos_abs2(f2 q) {
 #else
     const f2 s = mul2(t, rsq2(t));
 #endif
-    f2       p = fma2(B(-0.004307856317609549f), a, B(0.0192753653973341f));
-    p          = fma2(p, a, B(-0.044893890619277954f));
-    p          = fma2(p, a, B(0.08785323798656464f));
-    p          = fma2(p, a, B(-0.2145095020532608f));
-    p          = fma2(p, a, B(1.5707951784133911f));
+    const f2 p = acos_poly2<LSB>(a);
     return mul2(s, p);
 }
 // The two factors separately, the polynomial with its coefficients pre-multiplied
@@ -195,16 +215,13 @@ __device__ __forceinline__ void acos_parts2(f2 q, const acos_scaled& c, f2& s, f
 #ifndef DC_ACOS_FOLD_REFLECT
 #define DC_ACOS_FOLD_REFLECT 0
 #endif
+template <bool LSB = false>
 __device__ __forceinline__ f2 acos_signed2(f2 q) {
     const f2 a = make_float2(fminf(fabsf(q.x), DC_ONE_MINUS_DELTA),
                              fminf(fabsf(q.y), DC_ONE_MINUS_DELTA));
     const f2 t = sub2(B(1.0f), a);
     const f2 s = make_float2(mufu_sqrt(t.x), mufu_sqrt(t.y));
-    f2       p = fma2(B(-0.004307856317609549f), a, B(0.0192753653973341f));
-    p          = fma2(p, a, B(-0.044893890619277954f));
-    p          = fma2(p, a, B(0.08785323798656464f));
-    p          = fma2(p, a, B(-0.2145095020532608f));
-    p          = fma2(p, a, B(1.5707951784133911f));
+    const f2 p = acos_poly2<LSB>(a);
 #if DC_ACOS_FOLD_REFLECT
     const bool na = q.x < 0.0f, nb = q.y < 0.0f;
     const f2   ss  = make_float2(na ? -s.x : s.x, nb ? -s.y : s.y);
@@ -279,7 +296,7 @@ __device__ __forceinline__ bres bearing_core2(f2 b, f2 c, f2 bb, f2 cc, float co
     o.q        = div2(nom, d, (LSB_DIV && DC_U16_SKIP_REFINE) ? y : rcp_refine2(d, y));
 #endif
     if constexpr (WITH_ACOS)
-        o.r = acos_abs2(o.q);
+        o.r = acos_abs2<LSB_DIV>(o.q);
     return o;
 }
 

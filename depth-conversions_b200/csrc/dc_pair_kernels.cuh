@@ -283,7 +283,7 @@ __device__ __forceinline__ void max_curve_row(const kparams& p, const wrow<FEAT_
         auto pair = [&](f2 dm, f2 smm, f2 dp, f2 spp, float c1, float c2) {
             const bres k1 = bearing_core2<false, OUT == OUT_U16>(d0, dm, bb, smm, c1);
             const bres k2 = bearing_core2<false, OUT == OUT_U16>(d0, dp, bb, spp, c2);
-            const f2   s  = add2(acos_signed2(k1.q), acos_signed2(k2.q));
+            const f2   s  = add2(acos_signed2<OUT == OUT_U16>(k1.q), acos_signed2<OUT == OUT_U16>(k2.q));
             return make_float2((k1.bc.x != 0.0f && k2.bc.x != 0.0f) ? s.x : 0.0f,
                                (k1.bc.y != 0.0f && k2.bc.y != 0.0f) ? s.y : 0.0f);
         };
@@ -702,10 +702,11 @@ __device__ __forceinline__ edge edge_shared(f2 x, f2 y, f2 xx, f2 yy, float cu) 
 }
 #define DC_MC_INVALID (-1.0e30f)
 // bearing angle at pixel x towards pixel y over the shared edge e; yc = y * cos
+template <bool LSB = false>
 __device__ __forceinline__ f2 edge_end(f2 x, f2 yc, const edge& e) {
     const f2 nom = sub2(x, yc);
     const f2 q   = div2(nom, e.d, e.y);
-    const f2 a   = acos_signed2(q);
+    const f2 a   = acos_signed2<LSB>(q);
     return make_float2(e.bc.x != 0.0f ? a.x : DC_MC_INVALID, e.bc.y != 0.0f ? a.y : DC_MC_INVALID);
 }
 
@@ -891,9 +892,9 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
                 const float c = cs_(cs.h[j]);
                 const edge  e = edge_shared<!TAB, OUT == OUT_U16>(mid.r[j], mid.r[j + 1], mid.s[j], mid.s[j + 1], c);
                 if (j >= 1)  // pixel j looks right; angle_formula (:55-82): back + forward
-                    m[j - 1] = add2(hb, edge_end(mid.r[j], yc(mid, j + 1, c), e));
+                    m[j - 1] = add2(hb, edge_end<OUT == OUT_U16>(mid.r[j], yc(mid, j + 1, c), e));
                 if (j <= 3)  // pixel j+1 looks left
-                    hb = edge_end(mid.r[j + 1], yc(mid, j, c), e);
+                    hb = edge_end<OUT == OUT_U16>(mid.r[j + 1], yc(mid, j, c), e);
             }
         }
         auto take = [&](int i, f2 back, f2 fwd) {
@@ -907,8 +908,8 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
             const float co = cs_(cs.v[i]);
             const edge  e  = edge_shared<!TAB, OUT == OUT_U16>(mid.r[c], dn.r[c], mid.s[c], dn.s[c], co);
             if constexpr (STORE)
-                take(i, cget(i), edge_end(mid.r[c], yc(dn, c, co), e));
-            cset(i, edge_end(dn.r[c], yc(mid, c, co), e));
+                take(i, cget(i), edge_end<OUT == OUT_U16>(mid.r[c], yc(dn, c, co), e));
+            cset(i, edge_end<OUT == OUT_U16>(dn.r[c], yc(mid, c, co), e));
         }
         // diagonal edges (c, v) - (c+1, v+1), c = u0-1 .. u0+3: pixel c looks
         // down-right (forward), pixel c+1 of the next row up-left (carried)
@@ -920,11 +921,11 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
                 const edge  e  = edge_shared<!TAB, OUT == OUT_U16>(mid.r[c], dn.r[c + 1], mid.s[c], dn.s[c + 1], co);
                 if (c >= 1) {
                     if constexpr (STORE)
-                        take(c - 1, cget(4 + c - 1), edge_end(mid.r[c], yc(dn, c + 1, co), e));
+                        take(c - 1, cget(4 + c - 1), edge_end<OUT == OUT_U16>(mid.r[c], yc(dn, c + 1, co), e));
                     cset(4 + c - 1, pending);
                 }
                 if (c <= 3)
-                    pending = edge_end(dn.r[c + 1], yc(mid, c, co), e);
+                    pending = edge_end<OUT == OUT_U16>(dn.r[c + 1], yc(mid, c, co), e);
             }
         }
         // anti-diagonal edges (c, v) - (c-1, v+1), c = u0 .. u0+4: pixel c looks
@@ -937,20 +938,20 @@ __global__ void __launch_bounds__(kPairThreads, DC_MCE_BLOCKS)
                 const edge e = edge_shared<!TAB, OUT == OUT_U16>(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], cu);
                 if constexpr (STORE)
                     if (c <= 4)
-                        take(c - 1, cget(8 + c - 1), edge_end(mid.r[c], dn.c[c - 1], e));
+                        take(c - 1, cget(8 + c - 1), edge_end<OUT == OUT_U16>(mid.r[c], dn.c[c - 1], e));
                 if (c >= 2)
-                    cset(8 + c - 2, edge_end(dn.r[c - 1], mid.c[c], e));
+                    cset(8 + c - 2, edge_end<OUT == OUT_U16>(dn.r[c - 1], mid.c[c], e));
             } else {
                 if constexpr (STORE)
                     if (c <= 4) {
                         const float co = cs.d[c];  // D(u + 1, v + 1), u = u0 + c - 1
                         const edge  e  = edge_shared<!TAB, OUT == OUT_U16>(mid.r[c], dn.r[c - 1], mid.s[c], dn.s[c - 1], co);
-                        take(c - 1, cget(8 + c - 1), edge_end(mid.r[c], mul2(dn.r[c - 1], B(co)), e));
+                        take(c - 1, cget(8 + c - 1), edge_end<OUT == OUT_U16>(mid.r[c], mul2(dn.r[c - 1], B(co)), e));
                     }
                 if (c >= 2) {
                     const float co = cs.a[c - 2];  // A(u0 + c - 1, v)
                     const edge  e  = edge_shared<!TAB, OUT == OUT_U16>(dn.r[c - 1], mid.r[c], dn.s[c - 1], mid.s[c], co);
-                    cset(8 + c - 2, edge_end(dn.r[c - 1], mul2(mid.r[c], B(co)), e));
+                    cset(8 + c - 2, edge_end<OUT == OUT_U16>(dn.r[c - 1], mul2(mid.r[c], B(co)), e));
                 }
             }
         }

@@ -91,6 +91,23 @@ __global__ void check_acos_pair(unsigned long long* worst_bits) {
     atomicMax(worst_bits, (unsigned long long)__double_as_longlong(w));
 }
 
+// the degree-4 polynomial of the 16-bit kernels (dc_pair.cuh acos_poly2<true>): ABSOLUTE
+// error of the angle over every float in [-1, 1], in radians
+__global__ void check_acos_pair_u16(unsigned long long* worst_bits) {
+    const unsigned hi = __float_as_uint(1.0f);
+    double         w  = 0.0;
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+         i <= hi; i += (unsigned long long)gridDim.x * blockDim.x) {
+        const float  x  = __uint_as_float(unsigned(i));
+        const float2 r  = dc::pr::acos_signed2<true>(make_float2(x, -x));
+        const float  c  = 1.0f - 10.0f * 1.1920928955078125e-07f;
+        const double xc = double(fminf(x, c));
+        w = fmax(w, fabs(double(r.x) - acos(xc)));
+        w = fmax(w, fabs(double(r.y) - acos(-xc)));
+    }
+    atomicMax(worst_bits, (unsigned long long)__double_as_longlong(w));
+}
+
 // normalisation as flexion does it: component / sqrt(z), reciprocal shared and
 // seeded from the rsqrt of the square root step.
 __global__ void check_norm(unsigned long long* bad, unsigned long long n) {
@@ -181,7 +198,15 @@ int main() {
     double worst_pair;
     memcpy(&worst_pair, &wb, 8);
     printf("pair acos_signed2 exhaustive max_rel=%.3e\n", worst_pair);
-    const bool ok = bad == 0 && worst < 1e-6 && worst_pair < 2e-6;
+    cudaMemset(d, 0, 8);
+    check_acos_pair_u16<<<148 * 16, 256>>>(d);
+    cudaDeviceSynchronize();
+    cudaMemcpy(&wb, d, 8, cudaMemcpyDeviceToHost);
+    double worst_u16;
+    memcpy(&worst_u16, &wb, 8);
+    // 0.12 LSB of convert_bearing<ushort> (pi / 65535 = 4.79e-5 rad)
+    printf("pair acos_signed2<u16> exhaustive max_abs_rad=%.3e\n", worst_u16);
+    const bool ok = bad == 0 && worst < 1e-6 && worst_pair < 2e-6 && worst_u16 < 6e-6;
     printf("%s\n", ok ? "MATHCHECK OK" : "MATHCHECK FAILED");
     return ok ? 0 : 1;
 }
