@@ -74,6 +74,11 @@ cudaError_t launch_pair(const kparams& p, int n_frames, cudaStream_t s, launch_i
     static const int forced = env_int("DC_PAIR_SPEC", -1);  // debugging: 0 forces the generic kernel
     const int        spec   = half ? int(pr::SPEC_HALF) : forced == 0 ? 0 : pair_spec<FEAT, IN>(p);
     li.launches += 1;
+    if constexpr (FEAT == FEAT_BEARING && OUT == OUT_U16) {
+        // the 16-bit bearing epilogue has convert_bearing's factor compiled in
+        if (p.q_bearing != pr::kQBearing)
+            return cudaErrorInvalidValue;
+    }
     if constexpr (FEAT == FEAT_MAX_CURVE) {
         // The kernel that computes every pixel-pair edge once for both of its ends
         // (dc_pair_kernels.cuh maxcurve_edge_kernel): one scalar for all four

@@ -206,6 +206,31 @@ __device__ __forceinline__ void acos_parts2(f2 q, const acos_scaled& c, f2& s, f
     pk         = fma2(pk, a, B(c.k[0]));
 }
 #define DC_PI_F 3.14159274101257324f
+// convert_bearing<float, ushort>'s factor, conversion/util.h:71-79: 65535 / pi<float>. A
+// compile-time constant, so that the polynomial's coefficients times the factor are
+// immediates (dc_api.cu checks that kparams::q_bearing is this very float).
+constexpr float kQBearing = 65535.0f / DC_PI_F;
+// acos(min(|q|, 1 - delta)) * kQBearing = s * pk for the 16-bit bearing epilogue, which
+// multiplies s into the rounding FFMA2 (DC_BEARING_FOLD_Q): one FFMA2 less per angle pair.
+__device__ __forceinline__ void acos_parts_q2(f2 q, f2& s, f2& pk) {
+    const f2 a = make_float2(fminf(fabsf(q.x), DC_ONE_MINUS_DELTA),
+                             fminf(fabsf(q.y), DC_ONE_MINUS_DELTA));
+    const f2 t = sub2(B(1.0f), a);
+    s          = make_float2(mufu_sqrt(t.x), mufu_sqrt(t.y));
+    constexpr float K = kQBearing;
+#if DC_U16_ACOS_DEG == 4
+    pk = fma2(B(K * 0.009730911813676357f), a, B(K * -0.03761417418718338f));
+    pk = fma2(pk, a, B(K * 0.08563580363988876f));
+    pk = fma2(pk, a, B(K * -0.21428003907203674f));
+    pk = fma2(pk, a, B(K * 1.570791482925415f));
+#else
+    pk = fma2(B(K * -0.004307856317609549f), a, B(K * 0.0192753653973341f));
+    pk = fma2(pk, a, B(K * -0.044893890619277954f));
+    pk = fma2(pk, a, B(K * 0.08785323798656464f));
+    pk = fma2(pk, a, B(K * -0.2145095020532608f));
+    pk = fma2(pk, a, B(K * 1.5707951784133911f));
+#endif
+}
 // acos(clamp(q, -1 + delta, 1 - delta)), what the kernels call.
 // DC_ACOS_FOLD_REFLECT=1 puts the reflection inside the last FFMA2 (q < 0:
 // pi - s p = fma(-s, p, pi), else fma(s, p, 0)): one packed instruction less per

@@ -26,8 +26,12 @@ constexpr int kPairThreads = 128;
 #endif
 // 1: the u16 bearing epilogue multiplies the acos polynomial's coefficients by
 // 65535/pi and folds s * (Q P) into the rounding FFMA2 (16 FFMA2 per row less).
-// Measured no faster (0.5723 vs 0.5704 ms): the scaled coefficients are register
-// operands instead of immediates. Off.
+// Round 1 measured no gain with run-time scaled coefficients (register operands
+// instead of immediates, 0.5723 vs 0.5704 ms); round 2 made the factor a compile-time
+// constant (immediates again, dc_pair.cuh acos_parts_q2): still no gain (0.5215 vs
+// 0.5213 ms, 78 instead of 82 packed operations per pixel pair; the -s select costs what
+// the product saved). Off. What did pay is the constant itself: the +-Q / offset selects
+// of the epilogue take immediates (0.5307 -> 0.5213 ms).
 #ifndef DC_EDGE_RAD_FADD
 #define DC_EDGE_RAD_FADD 1
 #endif
@@ -185,7 +189,6 @@ __device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BE
                                             const wrow<FEAT_BEARING>& mid,
                                             const wrow<FEAT_BEARING>& dn,
                                             const rtabs<FEAT_BEARING>& tb, const pos& at) {
-    [[maybe_unused]] const acos_scaled aq = acos_scale(p.q_bearing);
     f2 sm[5];  // squares of the centre row: b*b of every pixel, c*c for horizontal
 #pragma unroll
     for (int i = 0; i < 5; ++i)
@@ -216,15 +219,15 @@ __device__ __forceinline__ void bearing_row(const kparams& p, const wrow<FEAT_BE
                 // and rounding afterwards this moves a result by at most one LSB
                 // (tolerance of the quantised images: +-1 LSB; acos itself is
                 // only 1e-6 accurate against glibc).
-                const float Q = p.q_bearing, M = 12582912.0f;
+                const float Q = kQBearing, M = 12582912.0f;
 #if DC_BEARING_FOLD_Q
-                // acos = s * P(a): the scale goes into the polynomial's coefficients
-                // (loop invariant), the reflection's sign onto s, and the product
+                // acos = s * P(a): the scale is inside the polynomial's (compile-time)
+                // coefficients, the reflection's sign goes onto s, and the product
                 // s * (Q P) happens inside the rounding FFMA2.
                 const float C  = fmaf(DC_PI_F, Q, M);
                 const bool  na = k.q.x < 0.0f, nb = k.q.y < 0.0f;
                 f2          s, pk;
-                acos_parts2(k.q, aq, s, pk);
+                acos_parts_q2(k.q, s, pk);
                 const f2 ss  = make_float2(na ? -s.x : s.x, nb ? -s.y : s.y);
                 const f2 off = make_float2(na ? C : M, nb ? C : M);
                 const f2 x   = fma2(ss, pk, off);
