@@ -102,6 +102,8 @@ inline size_t gauss_smem_bytes(int rx, int ry) {
            sizeof(float);
 }
 
+// 256 threads as 64 columns x 4 row groups: a thread walks its column (no index division);
+// a warp covers 32 consecutive columns of one row (conflict-free shared memory, coalesced).
 template <typename T>
 __global__ void __launch_bounds__(kGaussThreads)
     gaussian_blur_kernel(const T* __restrict__ in, T* __restrict__ out,
@@ -112,29 +114,37 @@ __global__ void __launch_bounds__(kGaussThreads)
     float*    tile = sm;            // ph x pw input pixels
     float*    rows = sm + ph * pw;  // ph x TW row-filtered values
     const int u0 = blockIdx.x * kGaussTW, v0 = blockIdx.y * kGaussTH;
+    const int tx = threadIdx.x & (kGaussTW - 1), ty = threadIdx.x / kGaussTW;  // 64 x 4
+    constexpr int TY = kGaussThreads / kGaussTW;
     const T*  src = in + size_t(blockIdx.z) * size_t(w) * h;
     T*        dst = out + size_t(blockIdx.z) * size_t(w) * h;
-    for (int i = threadIdx.x; i < ph * pw; i += kGaussThreads) {
-        const int y = i / pw, x = i - y * pw;
-        const int v = reflect101(v0 - ry + y, h), u = reflect101(u0 - rx + x, w);
-        tile[i]     = load_px(src + size_t(v) * w + u);
+    // a tile whose halo lies inside the image needs no border arithmetic
+    const bool inner = u0 - rx >= 0 && u0 + kGaussTW + rx <= w && v0 - ry >= 0 && v0 + kGaussTH + ry <= h;
+    for (int y = ty; y < ph; y += TY) {
+        const int v   = inner ? v0 - ry + y : reflect101(v0 - ry + y, h);
+        const T*  row = src + size_t(v) * w;
+        for (int x = tx; x < pw; x += kGaussTW) {
+            const int u      = inner ? u0 - rx + x : reflect101(u0 - rx + x, w);
+            tile[y * pw + x] = load_px(row + u);
+        }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < ph * kGaussTW; i += kGaussThreads) {
-        const int    y = i / kGaussTW, x = i - y * kGaussTW;
-        const float* c = tile + y * pw + x + rx;
+    for (int y = ty; y < ph; y += TY) {
+        const float* c = tile + y * pw + tx + rx;
         float        s = __fmul_rn(c[0], p.kx[0]);
         for (int k = 1; k <= rx; ++k)
             s = __fadd_rn(s, __fmul_rn(p.kx[k], __fadd_rn(c[k], c[-k])));
-        rows[i] = s;
+        rows[y * kGaussTW + tx] = s;
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < kGaussTH * kGaussTW; i += kGaussThreads) {
-        const int y = i / kGaussTW, x = i - y * kGaussTW;
-        const int u = u0 + x, v = v0 + y;
-        if (u >= w || v >= h)
-            continue;
-        const float* c = rows + (y + ry) * kGaussTW + x;
+    const int u = u0 + tx;
+    if (u >= w)
+        return;
+    for (int y = ty; y < kGaussTH; y += TY) {
+        const int v = v0 + y;
+        if (v >= h)
+            break;
+        const float* c = rows + (y + ry) * kGaussTW + tx;
         float        s = __fmul_rn(c[0], p.ky[0]);
         for (int k = 1; k <= ry; ++k)
             s = __fadd_rn(s, __fmul_rn(p.ky[k], __fadd_rn(c[k * kGaussTW], c[-k * kGaussTW])));
