@@ -299,7 +299,8 @@ __global__ void __launch_bounds__(kBilatThreads)
                     continue;
                 const float val   = c[dy * side + dx];
                 float       alpha = __fmul_rn(fabsf(__fsub_rn(val, val0)), scale);
-                const int   idx   = int(floorf(alpha));
+                // (<= kLutBins for finite input; the bound keeps an infinite pixel inside the table)
+                const int   idx   = min(int(floorf(alpha)), kLutBins);
                 alpha             = __fsub_rn(alpha, float(idx));
                 const float e0 = lut[idx], e1 = lut[idx + 1];
                 const float wgt =
