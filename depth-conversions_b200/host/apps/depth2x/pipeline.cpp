@@ -224,8 +224,8 @@ void run_device(const convert_spec& spec, int device, int first, int last, int b
         int next = first;
         while (next <= last) {
             // frames per batch: at most 256 MB per buffer and 64 frames, at least
-            // one frame per thread, and about six batches per job so that
-            // decoding, the GPU and encoding overlap even on short jobs
+            // one frame per thread, about six batches per job so that decoding, the
+            // GPU and encoding overlap even on short jobs, a multiple of the thread count
             int want = batch_size;
             if (want <= 0) {
                 const std::size_t px = spec.camera.model != 0
@@ -233,6 +233,11 @@ void run_device(const convert_spec& spec, int device, int first, int last, int b
                                            : std::size_t(1920) * 1080;
                 const int cap = int(std::clamp<std::size_t>((std::size_t(256) << 20) / (px * 2 * (1 + n_out)), 1, 64));
                 want = std::clamp(std::max((total + 5) / 6, threads), 1, cap);
+                // whole rounds of the codec pool: 17 frames on 16 threads decode and
+                // encode in two rounds, the second with one busy thread (measured on
+                // BASELINE config 1: 100 frames -> batches of 17)
+                if (want > threads)
+                    want -= want % threads;
             }
             const int n = std::min(want, last - next + 1);
             std::vector<pending_file> files{};
